@@ -1,0 +1,285 @@
+/* mundy_b200.h — C-ABI of the B200-native collision hot path (sm_100a).
+ *
+ * This header is the drop-in boundary: each entry point replaces one seam of the reference
+ * (MundyRepo/MuNDy @ 797a7f48; paths below are relative to the reference root). The reference has no FFI for this path
+ * (header-only C++20 templates over Kokkos), so the boundary is "what a maintainer would bind": plain pointers and
+ * sizes, no C++/torch types. INTEGRATION.md shows the reference-side stubs; include/mundy_b200/ holds the C++ veneer
+ * that keeps the reference's call signatures on top of these functions.
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer unless its name ends in _h (host) or the doc says otherwise.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream). Calls are asynchronous with respect
+ *     to the host except where a host-visible result is returned (documented per function).
+ *   - Layouts are the reference's: vectors are xyz-interleaved (3 doubles per item, `View<double*[3]>` LayoutRight /
+ *     STK field layout), quaternions are (w,x,y,z) (mundy/math/src/mundy_math/Quaternion.hpp), AABBs are
+ *     (min xyz, max xyz) (mundy/geom/src/mundy_geom/primitives/AABB.hpp:199-202), pairs are int32 (i,j).
+ *   - All arithmetic is fp64 with the reference's operation order and no FMA contraction.
+ *   - Return value: 0 = MB200_OK, negative = error (see enum); mb200_last_error_string() describes the last error of
+ *     the calling thread. Nothing throws or aborts across this boundary.
+ *   - Thread-safety: a handle is single-threaded; distinct handles / handle-free calls may be used concurrently.
+ *   - There is no CPU fallback: without a CUDA device every compute call returns MB200_ERR_CUDA.
+ */
+#ifndef MUNDY_B200_H_
+#define MUNDY_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MB200_ABI_VERSION 1
+
+enum mb200_status {
+  MB200_OK = 0,
+  MB200_ERR_INVALID_ARGUMENT = -1,
+  MB200_ERR_CUDA = -2,
+  MB200_ERR_CAPACITY = -3,       /* an output buffer supplied by the caller is too small */
+  MB200_ERR_NOT_CONVERGED = -4,  /* only returned where the reference would throw (see mb200_collision_step) */
+  MB200_ERR_COMM = -5
+};
+
+/* Body kinds. Sphere: centre + radius. Spherocylinder: centre + quaternion + radius + length, axis = q (x) z_hat
+ * (mundy/geom/src/mundy_geom/compute_aabb.hpp:115-117). */
+enum mb200_body_kind { MB200_SPHERE = 0, MB200_SPHEROCYLINDER = 1 };
+
+typedef void* mb200_stream;
+
+int mb200_abi_version(void);
+const char* mb200_last_error_string(void);
+/* Number of visible CUDA devices (0 when none / no driver). Host-only query. */
+int mb200_device_count(void);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * A. geom::compute_aabb, batched.   mundy/geom/src/mundy_geom/compute_aabb.hpp
+ * ------------------------------------------------------------------------------------------------------------- */
+/* compute_aabb(Sphere) :72-80.  center[3n], radius[n] -> aabb[6n] */
+int mb200_compute_aabb_sphere(mb200_stream stream, int64_t n, const double* center, const double* radius,
+                              double* aabb);
+/* compute_aabb(Spherocylinder) :106-127.  quat[4n] = (w,x,y,z), not assumed unit-norm. */
+int mb200_compute_aabb_spherocylinder(mb200_stream stream, int64_t n, const double* center, const double* quat,
+                                      const double* radius, const double* length, double* aabb);
+/* compute_aabb(SpherocylinderSegment) :130-143.  start[3n], end[3n]. */
+int mb200_compute_aabb_segment(mb200_stream stream, int64_t n, const double* start, const double* end,
+                               const double* radius, double* aabb);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * C. geom::distance (SharedNormalSigned), batched: item k of every array is one call of the reference function.
+ *    Output pointers may be NULL (that output is skipped).
+ * ------------------------------------------------------------------------------------------------------------- */
+/* distance(Sphere, Sphere, sep)  mundy/geom/src/mundy_geom/distance/SphereSphere.hpp:54-76 */
+int mb200_distance_sphere_sphere(mb200_stream stream, int64_t n, const double* c1, const double* r1, const double* c2,
+                                 const double* r2, double* dist, double* sep);
+/* distance(LineSegment, LineSegment, cp1, cp2, s, t, sep)  distance/LineSegmentLineSegment.hpp:189-318 */
+int mb200_distance_segment_segment(mb200_stream stream, int64_t n, const double* l0, const double* l1,
+                                   const double* m0, const double* m1, double* dist, double* s, double* t,
+                                   double* cp1, double* cp2, double* sep);
+/* distance(Point, LineSegment, cp, t, sep)  distance/PointLineSegment.hpp:128-172 (t unclamped, cp clamped) */
+int mb200_distance_point_segment(mb200_stream stream, int64_t n, const double* x, const double* p1, const double* p2,
+                                 double* dist, double* t, double* cp, double* sep);
+/* distance(LineSegment, Sphere, cp, t, sep)  distance/LineSegmentSphere.hpp:86-99 */
+int mb200_distance_segment_sphere(mb200_stream stream, int64_t n, const double* p1, const double* p2, const double* c,
+                                  const double* r, double* dist, double* t, double* cp, double* sep);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Body set in the caller's (reference) layout. kind/quat/length may be NULL when every body is a sphere.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct mb200_bodies {
+  int64_t n;
+  double* center;        /* [3n]  in/out for the step entry points, read-only elsewhere */
+  double* quat;          /* [4n]  (w,x,y,z) */
+  const double* radius;  /* [n] */
+  const double* length;  /* [n]   spherocylinder centre-line length */
+  const int32_t* kind;   /* [n]   mb200_body_kind */
+} mb200_bodies;
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * C5/K6. Narrow phase on a pair list: signed separation phi0, unit normal (from i to j), lever arms (centre-line
+ * closest point minus centre; zero for spheres). Restates the constraint initialisation of
+ * scrap/lcp_spheres/KokkosLCP.cpp:449-491 (spheres) and the composition of
+ * scrap/parameter_interface/linkers/.../SpherocylinderSpherocylinderLinker.cpp:207-247 with geom::distance (rods).
+ * pairs[2*npairs]; phi[npairs]; normal[3*npairs]; arm_i/arm_j[3*npairs] may be NULL.
+ * ------------------------------------------------------------------------------------------------------------- */
+int mb200_narrow_phase(mb200_stream stream, const mb200_bodies* bodies, int64_t npairs, const int32_t* pairs,
+                       double* phi, double* normal, double* arm_i, double* arm_j);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * B. Broad phase = mesh::GenNeighborLinks (mundy/mesh/src/mundy_mesh/GenNeighborLinkers.hpp:294-543), whose search
+ * call stk::search::coarse_search(MORTON_LBVH) (:650-664) is replaced by a Morton-sorted cell list on the device.
+ * Candidate predicate (fp64, exact): i<j and |c_j - c_i|^2 <= (S_i + S_j)^2, S = bounding radius + search buffer
+ * (:575-584); bounding radius = r (sphere) or L/2 + r (spherocylinder; geom/compute_bounding_radius.hpp:74-82).
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct mb200_neighbor_links mb200_neighbor_links; /* opaque; owns the pair list and the rebuild state */
+
+/* Search filters (GenNeighborLinkers.hpp:116-200 SearchFilterBase; applied by scan+scatter compaction :140-183). */
+enum mb200_search_filter {
+  MB200_FILTER_NONE = 0,           /* every bounding-sphere candidate becomes a link (the reference's default) */
+  MB200_FILTER_SHAPE_DISTANCE = 1  /* keep (i,j) iff surface separation <= 2*buffer: shapes inflated by the buffer
+                                      intersect. Identical to NONE for spheres; prunes rod pairs. */
+};
+
+int mb200_neighbor_links_create(mb200_neighbor_links** out);
+int mb200_neighbor_links_destroy(mb200_neighbor_links* h);
+/* Builder setters (set_search_buffer :455, set_search_filter :441, set_sort_search_results :427). */
+int mb200_neighbor_links_set_search_buffer(mb200_neighbor_links* h, double buffer);
+int mb200_neighbor_links_set_search_filter(mb200_neighbor_links* h, int filter);
+/* generate() :510-543. Rebuilds when never built, when n changed, when force != 0, or when some body moved more than
+ * half the buffer since the last build (:603-615). *rebuilt_h (host) receives 1/0. Synchronises the stream. */
+int mb200_neighbor_links_generate(mb200_neighbor_links* h, mb200_stream stream, const mb200_bodies* bodies, int force,
+                                  int* rebuilt_h);
+/* Number of links (host value; valid after generate). */
+int64_t mb200_neighbor_links_count(const mb200_neighbor_links* h);
+/* Copy the link list, in the caller's body indices, sorted by (i,j) with i<j, to pairs_out[2*capacity] (device). */
+int mb200_neighbor_links_get_pairs(mb200_neighbor_links* h, mb200_stream stream, int32_t* pairs_out, int64_t capacity);
+
+/* One-shot search on explicit search spheres (centre[3n], search radius S[n]): pairs sorted by (i,j).
+ * *count_h (host) receives the number found even when it exceeds capacity (then MB200_ERR_CAPACITY). */
+int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, const double* search_radius,
+                       int32_t* pairs_out, int64_t capacity, int64_t* count_h);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * D. Matrix-free contact operator (there is no assembled Jacobian in the reference).
+ *   D   : scrap/lcp_spheres/KokkosLCP.cpp:559-591   F_i -= gamma n, F_j += gamma n ; 6-DOF scrap/UnitTestMundy.cpp:652-674
+ *   M   : KokkosLCP.cpp:593-614, scrap/parameter_interface/NGPSpheresLCP.cpp:586-618 (U = F/(6 pi mu r));
+ *         rods scrap/UnitTestMundy.cpp:704-753
+ *   D^T : KokkosLCP.cpp:616-647 ; 6-DOF UnitTestMundy.cpp:783-824
+ * The scatter is done without atomics: body-major incidence lists + per-body ordered sums (deterministic).
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct mb200_contact_op {
+  int64_t n;              /* bodies */
+  int64_t npairs;         /* contacts */
+  const int32_t* pairs;   /* [2*npairs] */
+  const double* normal;   /* [3*npairs] */
+  const double* arm_i;    /* [3*npairs] or NULL => 3-DOF (spheres: force only) */
+  const double* arm_j;    /* [3*npairs] or NULL */
+  const double* quat;     /* [4n] or NULL => isotropic translational mobility */
+  const double* radius;   /* [n] */
+  const int32_t* kind;    /* [n] or NULL (all spheres) */
+  double viscosity;       /* mu */
+  double dt;
+} mb200_contact_op;
+
+/* F[3n] (and T[3n] when op->arm_i != NULL) = D gamma. */
+int mb200_apply_D(mb200_stream stream, const mb200_contact_op* op, const double* gamma, double* F, double* T);
+/* U = M F (and W = M_r T when T,W != NULL). Uses op->n, quat, radius, kind, viscosity only. */
+int mb200_apply_M(mb200_stream stream, const mb200_contact_op* op, const double* F, const double* T, double* U,
+                  double* W);
+/* gdot[npairs] = D^T (U, W). */
+int mb200_apply_DT(mb200_stream stream, const mb200_contact_op* op, const double* U, const double* W, double* gdot);
+/* y = dt * D^T M D x : the LinearOp `apply(x, y)` of math::convex (mundy/math/src/mundy_math/convex.hpp:186-191). */
+int mb200_apply_A(mb200_stream stream, const mb200_contact_op* op, const double* x, double* y);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * E1. Driver BBPGD  resolve_collisions  scrap/lcp_spheres/KokkosLCP.cpp:675-876 (+ external-velocity correction of
+ * scrap/parameter_interface/NGPSpheresLCP.cpp:751-759 when U_ext != NULL). SURVEY.md Appendix A is the statement.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct mb200_collision_result {  /* KokkosLCP.cpp:667-671 CollisionResult */
+  double max_abs_projected_sep;
+  int32_t ite_count;
+  int32_t converged;  /* max_abs_projected_sep < tol */
+  double max_displacement;
+} mb200_collision_result;
+
+typedef struct mb200_lcp_params {
+  double tol;
+  int32_t max_iters;
+  int32_t fixed_iters; /* >= 0: ignore tol, run exactly this many iterations (parity checks); < 0: off */
+} mb200_lcp_params;
+
+/* phi0[npairs] in/out (corrected in place by dt*D^T U_ext when U_ext != NULL); gamma[npairs] in/out;
+ * F,U[3n] out; T,W[3n] out when op->arm_i != NULL (else may be NULL). result_h is a HOST struct; synchronises. */
+int mb200_resolve_collisions(mb200_stream stream, const mb200_contact_op* op, const mb200_lcp_params* params,
+                             const double* U_ext, const double* W_ext, double* phi0, double* gamma, double* F,
+                             double* T, double* U, double* W, mb200_collision_result* result_h);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * E2. math::convex projected-gradient solver  mundy/math/src/mundy_math/convex.hpp
+ * ------------------------------------------------------------------------------------------------------------- */
+enum mb200_space_kind { MB200_SPACE_UNCONSTRAINED = 0, MB200_SPACE_LOWER = 1, MB200_SPACE_UPPER = 2, MB200_SPACE_BOX = 3 };
+enum mb200_residual_kind {
+  MB200_RESID_PROJECTED_DIFF = 0, /* LinfNormProjectedDiffResidual :468-496 (default) */
+  MB200_RESID_PROJECTED_GRAD = 1  /* LinfNormProjectedGradientResidual :434-466 */
+};
+typedef struct mb200_pgd_config { /* PGDConfig :519-525 */
+  uint32_t max_iters;             /* default 1000 */
+  double tol;                     /* default 1e-8 */
+  int32_t space_kind;
+  double lo, hi;
+  int32_t residual_kind;
+} mb200_pgd_config;
+typedef struct mb200_solve_result { /* SolveResult :527-541 */
+  uint32_t num_iters;
+  double residual;
+  int32_t converged;
+} mb200_solve_result;
+
+/* KokkosBackend pieces (:141-285) on device vectors: the static interface of the B200 backend in the C++ veneer. */
+int mb200_vec_axpby(mb200_stream stream, int64_t n, double alpha, const double* x, double beta, double* y);
+int mb200_vec_wrapped_axpbyz(mb200_stream stream, int64_t n, double alpha, const double* x, double beta,
+                             const double* y, double* z, int space_kind, double lo, double hi);
+/* sum (x - x_old)^2 -> *out_h ; sum (x - x_old)(g - g_old) -> *out_h   (both synchronise) */
+int mb200_vec_diff_dot(mb200_stream stream, int64_t n, const double* x, const double* x_old, double* out_h);
+int mb200_vec_diff_dot2(mb200_stream stream, int64_t n, const double* x, const double* x_old, const double* g,
+                        const double* g_old, double* out_h);
+int mb200_vec_residual(mb200_stream stream, int64_t n, const double* x, const double* g, int residual_kind,
+                       int space_kind, double lo, double hi, double* out_h);
+/* y = A x for a dense row-major n x n matrix (the KokkosBlas::gemv path, :166-184). */
+int mb200_dense_gemv(mb200_stream stream, int64_t n, const double* A, const double* x, double* y);
+
+/* solve_cqpp / solve_lcp (:789-845) with a dense A (row-major n x n) ... */
+int mb200_solve_cqpp_dense(mb200_stream stream, int64_t n, const double* A, const double* q, double* x,
+                           const mb200_pgd_config* cfg, mb200_solve_result* result_h);
+/* ... and with the collision operator A = dt D^T M D, q = phi0, x = gamma >= 0. */
+int mb200_solve_lcp_contact(mb200_stream stream, const mb200_contact_op* op, const double* phi0, double* gamma,
+                            const mb200_pgd_config* cfg, mb200_solve_result* result_h);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * E3. Euler update  x += dt U (KokkosLCP.cpp:1015); rods: q <- math::rotate_quaternion(q, W, dt)
+ * (mundy/math/src/mundy_math/Quaternion.hpp:1359-1385). quat/kind/W may be NULL.
+ * ------------------------------------------------------------------------------------------------------------- */
+int mb200_euler_update(mb200_stream stream, int64_t n, double* center, double* quat, const int32_t* kind,
+                       const double* U, const double* W, double dt);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Whole collision timestep (the loop body of scrap/parameter_interface/NGPSpheresLCP.cpp:1135-1292):
+ *   generate links if needed -> narrow phase -> (phi0 += dt D^T U_ext) -> BBPGD -> U += U_ext -> Euler.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct mb200_step_params {
+  double viscosity;
+  double dt;
+  double tol;
+  int32_t max_iters;
+  int32_t fixed_iters;       /* < 0 off */
+  int32_t throw_on_max_iters; /* !=0: return MB200_ERR_NOT_CONVERGED when ite_count == max_iters (the STK drivers
+                                 throw, scrap/lcp_spheres/NGPSpheresLCP.cpp:745-747) */
+  int32_t force_rebuild;
+} mb200_step_params;
+
+typedef struct mb200_step_stats {
+  mb200_collision_result lcp;
+  int64_t num_links;       /* constraints in this step */
+  int32_t rebuilt;
+  int32_t kernel_launches; /* kernels of this library launched by the call */
+} mb200_step_stats;
+
+/* Optional per-body arrays (device): F_ext -> U_ext = M F_ext is added (NULL: none); outputs may be NULL.
+ * bodies->center / quat are advanced in place. stats_h is a HOST struct; synchronises the stream. */
+int mb200_collision_step(mb200_neighbor_links* links, mb200_stream stream, const mb200_bodies* bodies,
+                         const mb200_step_params* params, const double* F_ext, const double* T_ext, double* F_col,
+                         double* T_col, double* U_out, double* W_out, mb200_step_stats* stats_h);
+
+/* Same step through HOST buffers (every pointer in bodies_h and the optional arrays is a host pointer): copies the
+ * inputs to the device, runs mb200_collision_step, copies centres/quaternions (and optional outputs) back.
+ * This is the call a host application that keeps its fields on the CPU would make. */
+int mb200_collision_step_host(mb200_neighbor_links* links, mb200_stream stream, const mb200_bodies* bodies_h,
+                              const mb200_step_params* params, const double* F_ext_h, const double* T_ext_h,
+                              double* F_col_h, double* T_col_h, double* U_out_h, double* W_out_h,
+                              mb200_step_stats* stats_h);
+
+/* Total kernels launched by this library in the calling process (a monotone counter; for bench accounting). */
+int64_t mb200_kernel_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MUNDY_B200_H_ */
