@@ -27,6 +27,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 #define MB200_ABI_VERSION 1
 
@@ -279,6 +282,9 @@ int mb200_collision_step_host(mb200_neighbor_links* links, mb200_stream stream, 
 /* Total kernels launched by this library in the calling process (a monotone counter; for bench accounting). */
 int64_t mb200_kernel_launch_count(void);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,28 @@
+// Internal (non-ABI) interfaces shared between the translation units of libmundy_b200.so.
+#pragma once
+#include "common.cuh"
+
+namespace mb200 {
+
+// narrow_phase.cu ------------------------------------------------------------------------------------------------
+// Caller layout -> 32-byte body records (shapes.cuh). perm == NULL: identity. b1 == NULL: spheres only.
+int pack_bodies(cudaStream_t st, const mb200_bodies* b, const int32_t* perm, D4* b0, D4* b1);
+int narrow_phase_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const D4* b0, const D4* b1,
+                         double* phi, double* normal, double* arm_i, double* arm_j);
+
+// lcp.cu ---------------------------------------------------------------------------------------------------------
+// Body-major incidence lists of a pair list: for body b, list[ptr[b] .. ptr[b+1]) holds 2*contact+side in ascending
+// order (side 0: b is the first body of the pair, 1: the second).
+struct Incidence {
+  Scratch<int64_t> ptr;    // n + 1
+  Scratch<uint32_t> list;  // 2 * npairs
+};
+int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, Incidence* inc);
+
+// The BBPGD solve on an already-built incidence structure (used by mb200_resolve_collisions and the step).
+int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const Incidence& inc,
+                            const mb200_lcp_params* params, const double* U_ext, const double* W_ext, double* phi0,
+                            double* gamma, double* F, double* T, double* U, double* W,
+                            mb200_collision_result* result_h);
+
+}  // namespace mb200

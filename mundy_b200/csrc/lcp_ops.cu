@@ -1,0 +1,181 @@
+// D. Matrix-free contact operator entry points (caller layout) and the body-major incidence build.
+#include "internal.cuh"
+#include "lcp.cuh"
+#include "sort_scan.cuh"
+
+namespace mb200 {
+namespace {
+
+__global__ void __launch_bounds__(256) incidence_keys_kernel(int64_t m, const int32_t* __restrict__ pairs_flat,
+                                                             uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                                                             uint32_t* __restrict__ counts) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= m) return;
+  const uint32_t b = static_cast<uint32_t>(pairs_flat[k]);
+  keys[k] = b;
+  vals[k] = static_cast<uint32_t>(k);  // 2 * contact + side
+  atomicAdd(counts + b, 1u);
+}
+
+template <bool SIX>
+__global__ void __launch_bounds__(128)
+    apply_D_kernel(int64_t n, const int64_t* __restrict__ ptr, const uint32_t* __restrict__ list,
+                   const double* __restrict__ gamma, const double* __restrict__ normal,
+                   const double* __restrict__ arm_i, const double* __restrict__ arm_j, double* __restrict__ F,
+                   double* __restrict__ T) {
+  const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (b >= n) return;
+  V3 f, t;
+  body_wrench<SIX>(b, ptr, list, gamma, normal, arm_i, arm_j, f, t);
+  st3(F, b, f);
+  if (SIX) st3(T, b, t);
+}
+
+__global__ void __launch_bounds__(256)
+    apply_M_kernel(int64_t n, const double* __restrict__ quat, const double* __restrict__ radius,
+                   const int32_t* __restrict__ kind, double mu, const double* __restrict__ F,
+                   const double* __restrict__ T, double* __restrict__ U, double* __restrict__ W) {
+  const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (b >= n) return;
+  const Mob m = mobility_of(radius[b], mu);
+  const bool rod = quat && kind && kind[b] == MB200_SPHEROCYLINDER;
+  const Q4 q = rod ? ldq(quat, b) : Q4{1.0, 0.0, 0.0, 0.0};
+  const V3 f = ld3(F, b);
+  const V3 t = T ? ld3(T, b) : V3{0.0, 0.0, 0.0};
+  V3 u, w;
+  body_mobility(m, rod, q, f, t, u, w);
+  st3(U, b, u);
+  if (W) st3(W, b, w);
+}
+
+template <bool SIX>
+__global__ void __launch_bounds__(256)
+    apply_DT_kernel(int64_t npairs, const int2* __restrict__ pairs, const double* __restrict__ normal,
+                    const double* __restrict__ arm_i, const double* __restrict__ arm_j, const double* __restrict__ U,
+                    const double* __restrict__ W, double scale, double* __restrict__ gdot) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c >= npairs) return;
+  const int2 p = pairs[c];
+  const V3 n = ld3(normal, c);
+  V3 wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
+  if (SIX) {
+    wi = ld3(W, p.x), wj = ld3(W, p.y);
+    ai = ld3(arm_i, c), aj = ld3(arm_j, c);
+  }
+  const double g = contact_rate<SIX>(n, ld3(U, p.x), ld3(U, p.y), wi, wj, ai, aj);
+  gdot[c] = (scale == 1.0) ? g : g * scale;
+}
+
+int check_op(const mb200_contact_op* op) {
+  MB200_REQUIRE(op && op->n >= 0 && op->npairs >= 0, "bad contact op sizes");
+  if (op->npairs > 0) MB200_REQUIRE(op->pairs && op->normal, "contact op: null pairs/normal");
+  MB200_REQUIRE((op->arm_i == nullptr) == (op->arm_j == nullptr), "contact op: arm_i/arm_j must both be set or NULL");
+  MB200_REQUIRE(op->n < (int64_t(1) << 31) && op->npairs < (int64_t(1) << 30), "contact op too large for int32 ids");
+  return MB200_OK;
+}
+
+}  // namespace
+
+int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, Incidence* inc) {
+  const int64_t m = 2 * npairs;
+  MB200_TRY(inc->ptr.alloc(n + 1, st));
+  MB200_TRY(inc->list.alloc(m > 0 ? m : 1, st));
+  Scratch<uint32_t> counts, keys, keys_alt, vals_alt;
+  MB200_TRY(counts.alloc(n > 0 ? n : 1, st));
+  MB200_CUDA(cudaMemsetAsync(counts.p, 0, (n > 0 ? n : 1) * sizeof(uint32_t), st));
+  if (m > 0) {
+    MB200_TRY(keys.alloc(m, st));
+    MB200_TRY(keys_alt.alloc(m, st));
+    MB200_TRY(vals_alt.alloc(m, st));
+    incidence_keys_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, pairs, keys.p, inc->list.p, counts.p);
+    MB200_LAUNCHED();
+    int bits = 1;
+    while ((int64_t(1) << bits) < n) ++bits;
+    MB200_TRY(radix_sort_u32(st, m, keys.p, keys_alt.p, inc->list.p, vals_alt.p, bits));
+  }
+  MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, inc->ptr.p));
+  return MB200_OK;
+}
+
+}  // namespace mb200
+
+using namespace mb200;
+
+extern "C" {
+
+int mb200_apply_D(mb200_stream stream, const mb200_contact_op* op, const double* gamma, double* F, double* T) {
+  MB200_TRY(check_op(op));
+  if (op->n == 0) return MB200_OK;
+  const bool six = op->arm_i != nullptr;
+  MB200_REQUIRE(F && (!six || T) && (gamma || op->npairs == 0), "null pointer");
+  MB200_TRY(require_device());
+  cudaStream_t st = as_stream(stream);
+  Incidence inc;
+  MB200_TRY(build_incidence(st, op->n, op->npairs, op->pairs, &inc));
+  if (six)
+    apply_D_kernel<true><<<grid_for(op->n, 128), 128, 0, st>>>(op->n, inc.ptr.p, inc.list.p, gamma, op->normal,
+                                                              op->arm_i, op->arm_j, F, T);
+  else
+    apply_D_kernel<false><<<grid_for(op->n, 128), 128, 0, st>>>(op->n, inc.ptr.p, inc.list.p, gamma, op->normal,
+                                                               nullptr, nullptr, F, nullptr);
+  MB200_LAUNCHED();
+  return MB200_OK;
+}
+
+int mb200_apply_M(mb200_stream stream, const mb200_contact_op* op, const double* F, const double* T, double* U,
+                  double* W) {
+  MB200_REQUIRE(op && op->n >= 0, "bad contact op");
+  if (op->n == 0) return MB200_OK;
+  MB200_REQUIRE(op->radius && F && U && ((T == nullptr) == (W == nullptr)), "null pointer");
+  MB200_TRY(require_device());
+  apply_M_kernel<<<grid_for(op->n, 256), 256, 0, as_stream(stream)>>>(op->n, op->quat, op->radius, op->kind,
+                                                                     op->viscosity, F, T, U, W);
+  MB200_LAUNCHED();
+  return MB200_OK;
+}
+
+int mb200_apply_DT(mb200_stream stream, const mb200_contact_op* op, const double* U, const double* W, double* gdot) {
+  MB200_TRY(check_op(op));
+  if (op->npairs == 0) return MB200_OK;
+  const bool six = op->arm_i != nullptr;
+  MB200_REQUIRE(U && gdot && (!six || W), "null pointer");
+  MB200_TRY(require_device());
+  const int2* p2 = reinterpret_cast<const int2*>(op->pairs);
+  if (six)
+    apply_DT_kernel<true><<<grid_for(op->npairs, 256), 256, 0, as_stream(stream)>>>(
+        op->npairs, p2, op->normal, op->arm_i, op->arm_j, U, W, 1.0, gdot);
+  else
+    apply_DT_kernel<false><<<grid_for(op->npairs, 256), 256, 0, as_stream(stream)>>>(
+        op->npairs, p2, op->normal, nullptr, nullptr, U, nullptr, 1.0, gdot);
+  MB200_LAUNCHED();
+  return MB200_OK;
+}
+
+int mb200_apply_A(mb200_stream stream, const mb200_contact_op* op, const double* x, double* y) {
+  MB200_TRY(check_op(op));
+  if (op->npairs == 0) return MB200_OK;
+  MB200_REQUIRE(x && y && op->radius, "null pointer");
+  MB200_TRY(require_device());
+  cudaStream_t st = as_stream(stream);
+  const bool six = op->arm_i != nullptr;
+  Scratch<double> F, T, U, W;
+  MB200_TRY(F.alloc(3 * op->n, st));
+  MB200_TRY(U.alloc(3 * op->n, st));
+  if (six) {
+    MB200_TRY(T.alloc(3 * op->n, st));
+    MB200_TRY(W.alloc(3 * op->n, st));
+  }
+  MB200_TRY(mb200_apply_D(stream, op, x, F.p, six ? T.p : nullptr));
+  MB200_TRY(mb200_apply_M(stream, op, F.p, six ? T.p : nullptr, U.p, six ? W.p : nullptr));
+  const int2* p2 = reinterpret_cast<const int2*>(op->pairs);
+  if (six)
+    apply_DT_kernel<true><<<grid_for(op->npairs, 256), 256, 0, st>>>(op->npairs, p2, op->normal, op->arm_i, op->arm_j,
+                                                                    U.p, W.p, op->dt, y);
+  else
+    apply_DT_kernel<false><<<grid_for(op->npairs, 256), 256, 0, st>>>(op->npairs, p2, op->normal, nullptr, nullptr,
+                                                                     U.p, nullptr, op->dt, y);
+  MB200_LAUNCHED();
+  return MB200_OK;
+}
+
+}  // extern "C"
