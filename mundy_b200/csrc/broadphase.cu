@@ -1,0 +1,399 @@
+// B. Broad phase: the device replacement of mesh::GenNeighborLinks' search
+// (mundy/mesh/src/mundy_mesh/GenNeighborLinkers.hpp:510-543,564-664; stk::search::coarse_search is third-party).
+//
+//   search spheres {c, S}  ->  Morton key of the uniform-grid cell (edge >= 2 S_max)  ->  radix sort (key, body)
+//   -> bodies gathered into Morton order (32-byte records)  ->  dense cell table [start, end)
+//   -> one warp per body walks its <= 27 neighbour cells in ascending key order, 32 candidates per step read as one
+//      contiguous run of records, exact fp64 predicate, warp ballot + popc compaction
+//   -> count pass, exclusive scan, fill pass: pair list sorted by (i, j) in Morton-order indices, no atomics.
+// The optional shape-distance search filter (GenNeighborLinkers.hpp:116-200 SearchFilter) is fused into the same passes.
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#include "links.cuh"
+#include "shapes.cuh"
+#include "sort_scan.cuh"
+
+namespace mb200 {
+namespace {
+
+constexpr int kMaxBitsPerAxis = 8;  // dense cell table of at most 2^24 entries
+
+struct GridParams {
+  double lo[3];
+  double h;
+  int nc[3];
+  int bits;  // per axis
+};
+
+__device__ __host__ inline uint32_t spread3(uint32_t v) {  // 10 bits -> every third bit
+  v &= 0x3ffu;
+  v = (v | (v << 16)) & 0x030000ffu;
+  v = (v | (v << 8)) & 0x0300f00fu;
+  v = (v | (v << 4)) & 0x030c30c3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+// z is the most significant dimension, as in the reference's Z-order comparator (mundy/math/.../zmort.hpp:261-265).
+__device__ __host__ inline uint32_t morton3(uint32_t cx, uint32_t cy, uint32_t cz) {
+  return spread3(cx) | (spread3(cy) << 1) | (spread3(cz) << 2);
+}
+
+__device__ inline int cell_coord(double x, double lo, double h, int nc) {
+  const int v = static_cast<int>(floor((x - lo) / h));
+  return min(max(v, 0), nc - 1);
+}
+
+// Search spheres in the caller's order + per-CTA bounds partials (min xyz, max xyz, max S).
+__global__ void __launch_bounds__(256)
+    search_spheres_kernel(int64_t n, const double* __restrict__ center, const double* __restrict__ radius,
+                          const double* __restrict__ length, const int32_t* __restrict__ kind,
+                          const double* __restrict__ explicit_S, double buffer, D4* __restrict__ sr,
+                          double* __restrict__ partials) {
+  __shared__ double sh[33];
+  const double big = 1.7976931348623157e308;
+  double lo[3] = {big, big, big}, hi[3] = {-big, -big, -big}, smax = 0.0;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const V3 c = ld3(center, i);
+    double S;
+    if (explicit_S) {
+      S = explicit_S[i];
+    } else {
+      // bounding radius: r (compute_bounding_radius.hpp:61-64) or 0.5*L + r (:74-82); search sphere = + buffer
+      const bool rod = kind && kind[i] == MB200_SPHEROCYLINDER;
+      const double rb = rod ? 0.5 * length[i] + radius[i] : radius[i];
+      S = rb + buffer;
+    }
+    st256(sr + i, D4{c.x, c.y, c.z, S});
+    lo[0] = fmin(lo[0], c.x), lo[1] = fmin(lo[1], c.y), lo[2] = fmin(lo[2], c.z);
+    hi[0] = fmax(hi[0], c.x), hi[1] = fmax(hi[1], c.y), hi[2] = fmax(hi[2], c.z);
+    smax = fmax(smax, S);
+  }
+  double out[7];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    out[k] = -block_max(-lo[k], sh, -big);
+    out[3 + k] = block_max(hi[k], sh, -big);
+  }
+  out[6] = block_max(smax, sh, 0.0);
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < 7; ++k) partials[7 * blockIdx.x + k] = out[k];
+  }
+}
+
+__global__ void __launch_bounds__(256) cell_keys_kernel(int64_t n, const D4* __restrict__ sr, GridParams gp,
+                                                        uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const D4 s = ldg256(sr + i);
+  keys[i] = morton3(cell_coord(s.x, gp.lo[0], gp.h, gp.nc[0]), cell_coord(s.y, gp.lo[1], gp.h, gp.nc[1]),
+                    cell_coord(s.z, gp.lo[2], gp.h, gp.nc[2]));
+  vals[i] = static_cast<uint32_t>(i);
+}
+
+__global__ void __launch_bounds__(256) gather_records_kernel(int64_t n, const uint32_t* __restrict__ perm,
+                                                             const D4* __restrict__ src, D4* __restrict__ dst) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k < n) st256(dst + k, ldg256(src + perm[k]));
+}
+
+// cell_range[key] = {start, end} over the sorted keys (table pre-zeroed: empty cells have start == end == 0).
+__global__ void __launch_bounds__(256) cell_ranges_kernel(int64_t n, const uint32_t* __restrict__ keys,
+                                                          int2* __restrict__ cell_range) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint32_t key = keys[k];
+  if (k == 0 || keys[k - 1] != key) cell_range[key].x = static_cast<int>(k);
+  if (k == n - 1 || keys[k + 1] != key) cell_range[key].y = static_cast<int>(k + 1);
+}
+
+// One warp per body i (Morton order). FILL = false: counts[i] = number of kept pairs (i, j>i).
+// FILL = true: writes them at pairs[rowptr[i] ...] in ascending j.
+template <bool FILL, bool FILTER>
+__global__ void __launch_bounds__(256)
+    find_pairs_kernel(int64_t n, const D4* __restrict__ sr, const D4* __restrict__ b0, const D4* __restrict__ b1,
+                      const uint32_t* __restrict__ perm, const int2* __restrict__ cell_range, GridParams gp,
+                      double cutoff, uint32_t* __restrict__ counts, const int64_t* __restrict__ rowptr, int2* __restrict__ pairs) {
+  const int lane = threadIdx.x & 31;
+  const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  if (i >= n) return;
+  const D4 si = ldg256(sr + i);
+  D4 b0i{0, 0, 0, 0}, b1i{0, 0, 0, 0};
+  uint32_t pi = 0;
+  if (FILTER) {
+    b0i = ldg256(b0 + i);
+    b1i = ldg256(b1 + i);
+    pi = perm[i];
+  }
+  const int cx = cell_coord(si.x, gp.lo[0], gp.h, gp.nc[0]);
+  const int cy = cell_coord(si.y, gp.lo[1], gp.h, gp.nc[1]);
+  const int cz = cell_coord(si.z, gp.lo[2], gp.h, gp.nc[2]);
+  const uint32_t my_key = morton3(cx, cy, cz);
+  // lane l < 27 owns neighbour cell l
+  uint32_t nkey = 0xffffffffu;
+  int beg = 0, end = 0;
+  if (lane < 27) {
+    const int x = cx + (lane % 3) - 1, y = cy + ((lane / 3) % 3) - 1, z = cz + (lane / 9) - 1;
+    if (x >= 0 && y >= 0 && z >= 0 && x < gp.nc[0] && y < gp.nc[1] && z < gp.nc[2]) {
+      const uint32_t k = morton3(x, y, z);
+      if (k >= my_key) {  // bodies with a smaller key have a smaller index: never j > i
+        const int2 r = __ldg(cell_range + k);
+        beg = (k == my_key) ? static_cast<int>(i) + 1 : r.x;
+        end = r.y;
+        if (end > beg) nkey = k;
+      }
+    }
+  }
+  const bool valid = nkey != 0xffffffffu;
+  int rank = 0;  // ascending-key rank among the valid cells
+#pragma unroll
+  for (int m = 0; m < 27; ++m) {
+    const uint32_t km = __shfl_sync(0xffffffffu, nkey, m);
+    rank += (km < nkey) ? 1 : 0;
+  }
+  const int nvalid = __popc(__ballot_sync(0xffffffffu, valid));
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  int64_t out = FILL ? rowptr[i] : 0;
+  uint32_t total = 0;
+  for (int r = 0; r < nvalid; ++r) {
+    const int src = __ffs(__ballot_sync(0xffffffffu, valid && rank == r)) - 1;
+    const int cbeg = __shfl_sync(0xffffffffu, beg, src);
+    const int cend = __shfl_sync(0xffffffffu, end, src);
+    for (int j0 = cbeg; j0 < cend; j0 += 32) {
+      const int j = j0 + lane;
+      bool keep = false;
+      if (j < cend) {
+        keep = is_candidate(si, ldg256(sr + j));
+        if (FILTER && keep) {
+          // evaluate in the caller's (i<j) order so that the decision is bit-identical to the reference order
+          const D4 b0j = ldg256(b0 + j), b1j = ldg256(b1 + j);
+          const PairGeom g = (pi < perm[j]) ? pair_geometry<true>(b0i, b1i, b0j, b1j)
+                                            : pair_geometry<true>(b0j, b1j, b0i, b1i);
+          keep = g.sep <= cutoff;
+        }
+      }
+      const uint32_t m = __ballot_sync(0xffffffffu, keep);
+      if (FILL && keep) pairs[out + __popc(m & lt_mask)] = make_int2(static_cast<int>(i), j);
+      out += __popc(m);
+      total += __popc(m);
+    }
+  }
+  if (!FILL && lane == 0) counts[i] = total;
+}
+
+}  // namespace
+
+namespace {
+
+// any |c - c_at_build| > 0.5 * buffer (GenNeighborLinkers.hpp:603-615); with the shape filter the two centre-line
+// endpoints are tracked instead of the centre (a rotation moves a rod's surface without moving its bounding sphere).
+__global__ void __launch_bounds__(256)
+    moved_kernel(int64_t n, const double* __restrict__ center, const double* __restrict__ ref_center,
+                 const double* __restrict__ quat, const double* __restrict__ length, const int32_t* __restrict__ kind,
+                 const D4* __restrict__ ref_b1, double thresh, int32_t* __restrict__ flag) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const V3 c = ld3(center, i), c0 = ld3(ref_center, i);
+  bool moved;
+  if (ref_b1 && kind && kind[i] == MB200_SPHEROCYLINDER) {
+    const D4 r = ldg256(ref_b1 + i);
+    const V3 h0{r.x, r.y, r.z};
+    const V3 h = (0.5 * length[i]) * qrot(ldq(quat, i), V3{0.0, 0.0, 1.0});
+    const V3 da = (c - h) - (c0 - h0), db = (c + h) - (c0 + h0);
+    moved = sqrt(da.x * da.x + da.y * da.y + da.z * da.z) > thresh || sqrt(db.x * db.x + db.y * db.y + db.z * db.z) > thresh;
+  } else {
+    const double dx = c.x - c0.x, dy = c.y - c0.y, dz = c.z - c0.z;
+    moved = sqrt(dx * dx + dy * dy + dz * dz) > thresh;
+  }
+  if (moved) *flag = 1;
+}
+
+__global__ void __launch_bounds__(256) canonical_keys_kernel(int64_t npairs, const int2* __restrict__ pairs,
+                                                             const uint32_t* __restrict__ perm, int shift,
+                                                             uint64_t* __restrict__ keys) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c >= npairs) return;
+  const int2 p = pairs[c];
+  const uint32_t a = perm[p.x], b = perm[p.y];
+  const uint64_t lo = a < b ? a : b, hi = a < b ? b : a;
+  keys[c] = (lo << shift) | hi;
+}
+__global__ void __launch_bounds__(256) canonical_unpack_kernel(int64_t npairs, const uint64_t* __restrict__ keys,
+                                                               int shift, int2* __restrict__ out) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c >= npairs) return;
+  const uint64_t k = keys[c];
+  out[c] = make_int2(static_cast<int>(k >> shift), static_cast<int>(k & ((uint64_t(1) << shift) - 1)));
+}
+
+int bits_for(int64_t n) {
+  int bits = 1;
+  while ((int64_t(1) << bits) < n) ++bits;
+  return bits;
+}
+
+}  // namespace
+
+int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, const double* explicit_S) {
+  const int64_t n = b->n;
+  h->n = n;
+  h->npairs = 0;
+  h->rods = b->kind != nullptr;
+  h->built = true;
+  const bool filter = !explicit_S && h->filter == MB200_FILTER_SHAPE_DISTANCE && h->rods;
+  MB200_TRY(h->perm.reserve(n > 0 ? n : 1));
+  MB200_TRY(h->ref_center.reserve(3 * n + 1));
+  if (n == 0) return build_incidence(st, 0, 0, nullptr, &h->inc);
+  MB200_CUDA(cudaMemcpyAsync(h->ref_center.p, b->center, 3 * n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+
+  // 1. search spheres + bounds
+  Scratch<D4> sr, sr_s, b0c, b1c, b0s, b1s;
+  Scratch<double> partials;
+  const int bgrid = grid_for(n, 256, kSMs * 2);
+  MB200_TRY(sr.alloc(n, st));
+  MB200_TRY(sr_s.alloc(n, st));
+  MB200_TRY(partials.alloc(7 * static_cast<size_t>(bgrid), st));
+  search_spheres_kernel<<<bgrid, 256, 0, st>>>(n, b->center, b->radius, b->length, b->kind, explicit_S, h->buffer,
+                                               sr.p, partials.p);
+  MB200_LAUNCHED();
+  std::vector<double> hp(7 * static_cast<size_t>(bgrid));
+  MB200_CUDA(cudaMemcpyAsync(hp.data(), partials.p, hp.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  MB200_CUDA(cudaStreamSynchronize(st));
+  GridParams gp;
+  double lo[3] = {hp[0], hp[1], hp[2]}, hi[3] = {hp[3], hp[4], hp[5]}, smax = hp[6];
+  for (int k = 1; k < bgrid; ++k) {
+    for (int d = 0; d < 3; ++d) {
+      lo[d] = std::min(lo[d], hp[7 * k + d]);
+      hi[d] = std::max(hi[d], hp[7 * k + 3 + d]);
+    }
+    smax = std::max(smax, hp[7 * k + 6]);
+  }
+  for (int d = 0; d < 3; ++d) MB200_REQUIRE(std::isfinite(lo[d]) && std::isfinite(hi[d]), "non-finite body centre");
+  MB200_REQUIRE(std::isfinite(smax), "non-finite search radius");
+  // cell edge >= largest possible centre distance of a candidate pair (2 S_max), with a relative margin so that the
+  // floor() binning can never separate a candidate pair by more than one cell
+  double edge = 2.0 * smax * (1.0 + 1e-9);
+  if (!(edge > 0.0)) edge = 1.0;
+  for (;;) {
+    bool ok = true;
+    for (int d = 0; d < 3; ++d) {
+      const double cells = std::floor((hi[d] - lo[d]) / edge) + 1.0;
+      ok = ok && cells <= double(1 << kMaxBitsPerAxis);
+      gp.nc[d] = ok ? static_cast<int>(cells) : 0;
+    }
+    if (ok) break;
+    edge *= 2.0;  // larger cells stay correct, only slower
+  }
+  gp.h = edge;
+  for (int d = 0; d < 3; ++d) gp.lo[d] = lo[d];
+  gp.bits = bits_for(std::max(gp.nc[0], std::max(gp.nc[1], gp.nc[2])));
+  const int key_bits = 3 * gp.bits;
+  const int64_t table = int64_t(1) << key_bits;
+
+  // 2. Morton keys, sort, gather into Morton order
+  Scratch<uint32_t> keys, keys_alt, vals_alt;
+  MB200_TRY(keys.alloc(n, st));
+  MB200_TRY(keys_alt.alloc(n, st));
+  MB200_TRY(vals_alt.alloc(n, st));
+  cell_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, sr.p, gp, keys.p, h->perm.p);
+  MB200_LAUNCHED();
+  MB200_TRY(radix_sort_u32(st, n, keys.p, keys_alt.p, h->perm.p, vals_alt.p, key_bits));
+  gather_records_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, sr.p, sr_s.p);
+  MB200_LAUNCHED();
+  if (filter) {
+    MB200_TRY(b0s.alloc(n, st));
+    MB200_TRY(b1s.alloc(n, st));
+    MB200_TRY(pack_bodies(st, b, reinterpret_cast<const int32_t*>(h->perm.p), b0s.p, b1s.p));
+    MB200_TRY(h->ref_b1.reserve(n));
+    MB200_TRY(b0c.alloc(n, st));
+    MB200_TRY(pack_bodies(st, b, nullptr, b0c.p, h->ref_b1.p));
+  }
+
+  // 3. cell table
+  Scratch<int2> cell_range;
+  MB200_TRY(cell_range.alloc(table, st));
+  MB200_CUDA(cudaMemsetAsync(cell_range.p, 0, table * sizeof(int2), st));
+  cell_ranges_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, keys.p, cell_range.p);
+  MB200_LAUNCHED();
+
+  // 4. count -> scan -> fill
+  Scratch<uint32_t> counts;
+  Scratch<int64_t> rowptr;
+  MB200_TRY(counts.alloc(n, st));
+  MB200_TRY(rowptr.alloc(n + 1, st));
+  const double cutoff = 2.0 * h->buffer;
+  const int pgrid = grid_for(n * 32, 256);
+  if (filter)
+    find_pairs_kernel<false, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
+                                                         counts.p, nullptr, nullptr);
+  else
+    find_pairs_kernel<false, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
+                                                          cutoff, counts.p, nullptr, nullptr);
+  MB200_LAUNCHED();
+  MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, rowptr.p));
+  int64_t total = 0;
+  MB200_CUDA(cudaMemcpyAsync(&total, rowptr.p + n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  MB200_CUDA(cudaStreamSynchronize(st));
+  if (total >= (int64_t(1) << 30)) {
+    set_error("pair list exceeds 2^30 entries");
+    return MB200_ERR_CAPACITY;
+  }
+  h->npairs = total;
+  MB200_TRY(h->pairs.reserve(2 * total + 2));
+  if (total > 0) {
+    int2* out = reinterpret_cast<int2*>(h->pairs.p);
+    if (filter)
+      find_pairs_kernel<true, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
+                                                          nullptr, rowptr.p, out);
+    else
+      find_pairs_kernel<true, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
+                                                           cutoff, nullptr, rowptr.p, out);
+    MB200_LAUNCHED();
+  }
+  // 5. body-major incidence lists for the contact operator
+  return build_incidence(st, n, total, h->pairs.p, &h->inc);
+}
+
+int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, int force, int* rebuilt_h) {
+  bool rebuild = force || !h->built || h->n != b->n;
+  if (!rebuild && b->n > 0) {
+    MB200_TRY(h->flag.reserve(1));
+    MB200_CUDA(cudaMemsetAsync(h->flag.p, 0, sizeof(int32_t), st));
+    const bool shape = h->filter == MB200_FILTER_SHAPE_DISTANCE && h->rods;
+    moved_kernel<<<grid_for(b->n, 256), 256, 0, st>>>(b->n, b->center, h->ref_center.p, b->quat, b->length, b->kind,
+                                                     shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p);
+    MB200_LAUNCHED();
+    int32_t moved = 0;
+    MB200_CUDA(cudaMemcpyAsync(&moved, h->flag.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    MB200_CUDA(cudaStreamSynchronize(st));
+    rebuild = moved != 0;
+  }
+  if (rebuild) MB200_TRY(build_links(st, h, b, nullptr));
+  if (rebuilt_h) *rebuilt_h = rebuild ? 1 : 0;
+  return MB200_OK;
+}
+
+}  // namespace mb200
+
+namespace mb200 {
+
+int canonical_pairs(cudaStream_t st, mb200_neighbor_links* h, int32_t* out) {
+  const int64_t C = h->npairs;
+  if (C == 0) return MB200_OK;
+  const int shift = bits_for(h->n);
+  Scratch<uint64_t> keys, keys_alt;
+  MB200_TRY(keys.alloc(C, st));
+  MB200_TRY(keys_alt.alloc(C, st));
+  canonical_keys_kernel<<<grid_for(C, 256), 256, 0, st>>>(C, reinterpret_cast<const int2*>(h->pairs.p), h->perm.p,
+                                                         shift, keys.p);
+  MB200_LAUNCHED();
+  MB200_TRY(radix_sort_u64(st, C, keys.p, keys_alt.p, nullptr, nullptr, 2 * shift));
+  canonical_unpack_kernel<<<grid_for(C, 256), 256, 0, st>>>(C, keys.p, shift, reinterpret_cast<int2*>(out));
+  MB200_LAUNCHED();
+  return MB200_OK;
+}
+
+}  // namespace mb200

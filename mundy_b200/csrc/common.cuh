@@ -266,6 +266,24 @@ __host__ __device__ inline double dist_segseg(const V3& l0, const V3& l1, const 
   return dist_pp(cp1, cp2, sep);
 }
 
+// math::rotate_quaternion(q, omega, dt)  mundy/math/src/mundy_math/Quaternion.hpp:1359-1385 (Delong 2015 App. A)
+__device__ inline Q4 rotate_quaternion(const Q4& q, const V3& om, double dt) {
+  const double w = norm(om);
+  if (w < kZeroTol) return q;
+  const double winv = 1.0 / w;
+  const double sw = sin(0.5 * w * dt);
+  const double cw = cos(0.5 * w * dt);
+  const double s = q.w;
+  const V3 p{q.x, q.y, q.z};
+  const V3 t1 = ((s * sw) * om) * winv;
+  const V3 t2 = cw * p;
+  const V3 t3 = (sw * winv) * cross(om, p);
+  const V3 xyz = (t1 + t2) + t3;
+  const double qw = s * cw - dot(om, p) * sw * winv;
+  const double inv_norm = 1.0 / sqrt(qw * qw + xyz.x * xyz.x + xyz.y * xyz.y + xyz.z * xyz.z);
+  return Q4{qw * inv_norm, xyz.x * inv_norm, xyz.y * inv_norm, xyz.z * inv_norm};
+}
+
 // ---- warp / block reductions (fixed order => run-to-run deterministic) -----------------------------------------
 __device__ inline double warp_sum(double v) {
 #pragma unroll

@@ -26,3 +26,9 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
                             mb200_collision_result* result_h);
 
 }  // namespace mb200
+
+namespace mb200 {
+// euler.cu
+int euler_update(cudaStream_t st, int64_t n, double* center, double* quat, const int32_t* kind, const double* U,
+                 const double* W, double dt);
+}  // namespace mb200
