@@ -1,0 +1,268 @@
+"""Thin torch-facing wrappers over the C-ABI (torch supplies device memory and streams; nothing is computed here).
+
+Every function takes CUDA float64/int32 tensors in the reference's layouts and forwards their data pointers to
+libmundy_b200.so. They fail loudly (Mb200Error) when no GPU is present: there is no CPU path.
+"""
+import ctypes as C
+
+import torch
+
+from . import _capi as capi
+from ._capi import lib, check
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "expected a contiguous CUDA tensor"
+    return C.c_void_p(t.data_ptr())
+
+
+def _f64(t):
+    assert t is None or t.dtype == torch.float64
+    return _p(t)
+
+
+def _i32(t):
+    assert t is None or t.dtype == torch.int32
+    return _p(t)
+
+
+def _new(n, like, dtype=torch.float64):
+    return torch.empty(n, dtype=dtype, device=like.device)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def compute_aabb_sphere(center, radius):
+    n = radius.numel()
+    out = _new((n, 6), center)
+    check(lib.mb200_compute_aabb_sphere(_stream(), n, _f64(center), _f64(radius), _f64(out)), "compute_aabb_sphere")
+    return out
+
+
+def compute_aabb_spherocylinder(center, quat, radius, length):
+    n = radius.numel()
+    out = _new((n, 6), center)
+    check(lib.mb200_compute_aabb_spherocylinder(_stream(), n, _f64(center), _f64(quat), _f64(radius), _f64(length),
+                                                _f64(out)), "compute_aabb_spherocylinder")
+    return out
+
+
+def compute_aabb_segment(start, end, radius):
+    n = radius.numel()
+    out = _new((n, 6), start)
+    check(lib.mb200_compute_aabb_segment(_stream(), n, _f64(start), _f64(end), _f64(radius), _f64(out)),
+          "compute_aabb_segment")
+    return out
+
+
+def distance_sphere_sphere(c1, r1, c2, r2):
+    n = r1.numel()
+    dist, sep = _new(n, c1), _new((n, 3), c1)
+    check(lib.mb200_distance_sphere_sphere(_stream(), n, _f64(c1), _f64(r1), _f64(c2), _f64(r2), _f64(dist),
+                                           _f64(sep)), "distance_sphere_sphere")
+    return dist, sep
+
+
+def distance_segment_segment(l0, l1, m0, m1):
+    n = l0.shape[0]
+    dist, s, t = _new(n, l0), _new(n, l0), _new(n, l0)
+    cp1, cp2, sep = _new((n, 3), l0), _new((n, 3), l0), _new((n, 3), l0)
+    check(lib.mb200_distance_segment_segment(_stream(), n, _f64(l0), _f64(l1), _f64(m0), _f64(m1), _f64(dist), _f64(s),
+                                             _f64(t), _f64(cp1), _f64(cp2), _f64(sep)), "distance_segment_segment")
+    return dist, s, t, cp1, cp2, sep
+
+
+def distance_point_segment(x, p1, p2):
+    n = x.shape[0]
+    dist, t, cp, sep = _new(n, x), _new(n, x), _new((n, 3), x), _new((n, 3), x)
+    check(lib.mb200_distance_point_segment(_stream(), n, _f64(x), _f64(p1), _f64(p2), _f64(dist), _f64(t), _f64(cp),
+                                           _f64(sep)), "distance_point_segment")
+    return dist, t, cp, sep
+
+
+def distance_segment_sphere(p1, p2, c, r):
+    n = r.numel()
+    dist, t, cp, sep = _new(n, c), _new(n, c), _new((n, 3), c), _new((n, 3), c)
+    check(lib.mb200_distance_segment_sphere(_stream(), n, _f64(p1), _f64(p2), _f64(c), _f64(r), _f64(dist), _f64(t),
+                                            _f64(cp), _f64(sep)), "distance_segment_sphere")
+    return dist, t, cp, sep
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def make_bodies(center, radius, quat=None, length=None, kind=None):
+    b = capi.Bodies(radius.numel(), _f64(center), _f64(quat), _f64(radius), _f64(length), _i32(kind))
+    b._keep = (center, radius, quat, length, kind)
+    return b
+
+
+def narrow_phase(bodies, pairs, arms=False):
+    npairs = pairs.shape[0]
+    ref = bodies._keep[0]
+    phi, normal = _new(npairs, ref), _new((npairs, 3), ref)
+    ai = _new((npairs, 3), ref) if arms else None
+    aj = _new((npairs, 3), ref) if arms else None
+    check(lib.mb200_narrow_phase(_stream(), C.byref(bodies), npairs, _i32(pairs), _f64(phi), _f64(normal), _f64(ai),
+                                 _f64(aj)), "narrow_phase")
+    return phi, normal, ai, aj
+
+
+def search_pairs(center, search_radius, capacity=None):
+    n = search_radius.numel()
+    count = C.c_int64(0)
+    if capacity is None:
+        capacity = max(64 * n, 1024)
+    out = torch.empty((capacity, 2), dtype=torch.int32, device=center.device)
+    st = lib.mb200_search_pairs(_stream(), n, _f64(center), _f64(search_radius), _i32(out), capacity, C.byref(count))
+    if st == -3:  # capacity: retry with the exact size
+        out = torch.empty((count.value, 2), dtype=torch.int32, device=center.device)
+        st = lib.mb200_search_pairs(_stream(), n, _f64(center), _f64(search_radius), _i32(out), count.value,
+                                    C.byref(count))
+    check(st, "search_pairs")
+    return out[: count.value]
+
+
+class NeighborLinks:
+    """mesh::GenNeighborLinks-like builder (mundy/mesh/src/mundy_mesh/GenNeighborLinkers.hpp:294-543)."""
+
+    FILTER_NONE = 0
+    FILTER_SHAPE_DISTANCE = 1
+
+    def __init__(self):
+        self._h = C.c_void_p()
+        check(lib.mb200_neighbor_links_create(C.byref(self._h)), "neighbor_links_create")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.mb200_neighbor_links_destroy(self._h)
+            self._h = None
+
+    def set_search_buffer(self, buffer):
+        check(lib.mb200_neighbor_links_set_search_buffer(self._h, float(buffer)), "set_search_buffer")
+        return self
+
+    def set_search_filter(self, filt):
+        check(lib.mb200_neighbor_links_set_search_filter(self._h, int(filt)), "set_search_filter")
+        return self
+
+    def generate(self, bodies, force=False):
+        rebuilt = C.c_int(0)
+        check(lib.mb200_neighbor_links_generate(self._h, _stream(), C.byref(bodies), int(force), C.byref(rebuilt)),
+              "neighbor_links_generate")
+        return bool(rebuilt.value)
+
+    def count(self):
+        return lib.mb200_neighbor_links_count(self._h)
+
+    def pairs(self, device="cuda"):
+        n = self.count()
+        out = torch.empty((n, 2), dtype=torch.int32, device=device)
+        check(lib.mb200_neighbor_links_get_pairs(self._h, _stream(), _i32(out), n), "neighbor_links_get_pairs")
+        return out
+
+    def step(self, bodies, viscosity, dt, tol, max_iters, fixed_iters=-1, throw_on_max_iters=False,
+             force_rebuild=False, F_ext=None, T_ext=None, F_col=None, T_col=None, U_out=None, W_out=None):
+        params = capi.StepParams(viscosity, dt, tol, max_iters, fixed_iters, int(throw_on_max_iters),
+                                 int(force_rebuild))
+        stats = capi.StepStats()
+        check(lib.mb200_collision_step(self._h, _stream(), C.byref(bodies), C.byref(params), _f64(F_ext), _f64(T_ext),
+                                       _f64(F_col), _f64(T_col), _f64(U_out), _f64(W_out), C.byref(stats)),
+              "collision_step")
+        return stats
+
+    def step_host(self, center, radius, quat, length, kind, viscosity, dt, tol, max_iters, fixed_iters=-1,
+                  F_ext=None, T_ext=None, F_col=None, T_col=None, U_out=None, W_out=None, force_rebuild=False):
+        """Host (CPU, ideally pinned) tensors in, advanced in place. H2D + step + D2H inside the call."""
+        def hp(t):
+            if t is None:
+                return None
+            assert (not t.is_cuda) and t.is_contiguous()
+            return C.c_void_p(t.data_ptr())
+        b = capi.Bodies(radius.numel(), hp(center), hp(quat), hp(radius), hp(length), hp(kind))
+        params = capi.StepParams(viscosity, dt, tol, max_iters, fixed_iters, 0, int(force_rebuild))
+        stats = capi.StepStats()
+        check(lib.mb200_collision_step_host(self._h, _stream(), C.byref(b), C.byref(params), hp(F_ext), hp(T_ext),
+                                            hp(F_col), hp(T_col), hp(U_out), hp(W_out), C.byref(stats)),
+              "collision_step_host")
+        return stats
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def make_contact_op(n, pairs, normal, radius, viscosity, dt, arm_i=None, arm_j=None, quat=None, kind=None):
+    op = capi.ContactOp(n, pairs.shape[0], _i32(pairs), _f64(normal), _f64(arm_i), _f64(arm_j), _f64(quat),
+                        _f64(radius), _i32(kind), viscosity, dt)
+    op._keep = (pairs, normal, arm_i, arm_j, quat, radius, kind)
+    return op
+
+
+def apply_D(op, gamma):
+    dev = gamma.device
+    six = bool(op.arm_i)
+    F = torch.empty((op.n, 3), dtype=torch.float64, device=dev)
+    T = torch.empty((op.n, 3), dtype=torch.float64, device=dev) if six else None
+    check(lib.mb200_apply_D(_stream(), C.byref(op), _f64(gamma), _f64(F), _f64(T)), "apply_D")
+    return F, T
+
+
+def apply_M(op, F, T=None):
+    U = torch.empty_like(F)
+    W = torch.empty_like(T) if T is not None else None
+    check(lib.mb200_apply_M(_stream(), C.byref(op), _f64(F), _f64(T), _f64(U), _f64(W)), "apply_M")
+    return U, W
+
+
+def apply_DT(op, U, W=None):
+    g = torch.empty(op.npairs, dtype=torch.float64, device=U.device)
+    check(lib.mb200_apply_DT(_stream(), C.byref(op), _f64(U), _f64(W), _f64(g)), "apply_DT")
+    return g
+
+
+def apply_A(op, x):
+    y = torch.empty_like(x)
+    check(lib.mb200_apply_A(_stream(), C.byref(op), _f64(x), _f64(y)), "apply_A")
+    return y
+
+
+def resolve_collisions(op, phi0, gamma, tol, max_iters, fixed_iters=-1, U_ext=None, W_ext=None):
+    """phi0 and gamma are updated in place. Returns (result, F, T, U, W)."""
+    dev = phi0.device
+    six = bool(op.arm_i)
+    F = torch.empty((op.n, 3), dtype=torch.float64, device=dev)
+    U = torch.empty((op.n, 3), dtype=torch.float64, device=dev)
+    T = torch.empty((op.n, 3), dtype=torch.float64, device=dev) if six else None
+    W = torch.empty((op.n, 3), dtype=torch.float64, device=dev) if six else None
+    params = capi.LcpParams(tol, max_iters, fixed_iters)
+    res = capi.CollisionResult()
+    check(lib.mb200_resolve_collisions(_stream(), C.byref(op), C.byref(params), _f64(U_ext), _f64(W_ext), _f64(phi0),
+                                       _f64(gamma), _f64(F), _f64(T), _f64(U), _f64(W), C.byref(res)),
+          "resolve_collisions")
+    return res, F, T, U, W
+
+
+def solve_cqpp_dense(A, q, x, max_iters=1000, tol=1e-8, space_kind=1, lo=0.0, hi=0.0, residual_kind=0):
+    cfg = capi.PgdConfig(max_iters, tol, space_kind, lo, hi, residual_kind)
+    res = capi.SolveResult()
+    check(lib.mb200_solve_cqpp_dense(_stream(), q.numel(), _f64(A), _f64(q), _f64(x), C.byref(cfg), C.byref(res)),
+          "solve_cqpp_dense")
+    return res
+
+
+def solve_lcp_contact(op, phi0, gamma, max_iters=1000, tol=1e-8, residual_kind=0):
+    cfg = capi.PgdConfig(max_iters, tol, 1, 0.0, 0.0, residual_kind)
+    res = capi.SolveResult()
+    check(lib.mb200_solve_lcp_contact(_stream(), C.byref(op), _f64(phi0), _f64(gamma), C.byref(cfg), C.byref(res)),
+          "solve_lcp_contact")
+    return res
+
+
+def euler_update(center, U, dt, quat=None, kind=None, W=None):
+    check(lib.mb200_euler_update(_stream(), center.shape[0], _f64(center), _f64(quat), _i32(kind), _f64(U), _f64(W),
+                                 dt), "euler_update")
+
+
+def kernel_launch_count():
+    return lib.mb200_kernel_launch_count()

@@ -1,0 +1,272 @@
+"""numpy/ctypes front-end to the CPU oracle (oracle/liboracle.so) and, when present, to the reference's own headers
+compiled behind the Kokkos shim (oracle/_ref/libmundy_ref.so). TEST INFRASTRUCTURE ONLY: only tests/, smoke() and
+bench.py's cpu_baseline / --impl reference legs may import this."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_SO = os.path.join(ORACLE_DIR, "liboracle.so")
+REF_SO = os.path.join(ORACLE_DIR, "_ref", "libmundy_ref.so")
+
+
+def _build():
+    if not os.path.exists(ORACLE_SO) or (os.path.isdir("/root/reference/mundy") and not os.path.exists(REF_SO)):
+        subprocess.run(["make", "-C", ORACLE_DIR, "all"], check=True, capture_output=True)
+
+
+_build()
+orc = C.CDLL(ORACLE_SO)
+ref = C.CDLL(REF_SO) if os.path.exists(REF_SO) else None
+
+_d = np.float64
+_i = np.int32
+
+
+def _a(x, dtype=_d):
+    return None if x is None else np.ascontiguousarray(x, dtype=dtype)
+
+
+def _p(x):
+    return None if x is None else x.ctypes.data_as(C.c_void_p)
+
+
+class CollisionResult(C.Structure):
+    _fields_ = [("max_abs_projected_sep", C.c_double), ("ite_count", C.c_int), ("max_displacement", C.c_double)]
+
+
+class ContactOpCtx(C.Structure):
+    _fields_ = [("n", C.c_long), ("npairs", C.c_long), ("pairs", C.c_void_p), ("normal", C.c_void_p),
+                ("arm_i", C.c_void_p), ("arm_j", C.c_void_p), ("quat", C.c_void_p), ("r", C.c_void_p),
+                ("kind", C.c_void_p), ("mu", C.c_double), ("dt", C.c_double)]
+
+
+def _call(lib, name, *args, restype=None):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    conv = []
+    for a in args:
+        if isinstance(a, np.ndarray) or a is None:
+            conv.append(_p(a))
+        elif isinstance(a, float):
+            conv.append(C.c_double(a))
+        elif isinstance(a, (int, np.integer)):
+            conv.append(C.c_long(int(a)))
+        else:
+            conv.append(a)
+    return fn(*conv)
+
+
+# ---- leaves (available from both libraries: prefix orc_ / ref_) ---------------------------------------------------
+def aabb_sphere(pos, r, lib=None, prefix="orc_"):
+    lib = lib or orc
+    pos, r = _a(pos), _a(r)
+    out = np.empty((len(r), 6))
+    _call(lib, prefix + "aabb_sphere", len(r), pos, r, out)
+    return out
+
+
+def aabb_spherocylinder(pos, quat, r, length, lib=None, prefix="orc_"):
+    lib = lib or orc
+    pos, quat, r, length = _a(pos), _a(quat), _a(r), _a(length)
+    out = np.empty((len(r), 6))
+    _call(lib, prefix + "aabb_spherocylinder", len(r), pos, quat, r, length, out)
+    return out
+
+
+def aabb_segment(p0, p1, r, lib=None, prefix="orc_"):
+    lib = lib or orc
+    p0, p1, r = _a(p0), _a(p1), _a(r)
+    out = np.empty((len(r), 6))
+    _call(lib, prefix + "aabb_segment", len(r), p0, p1, r, out)
+    return out
+
+
+def quat_rotate(quat, v, lib=None, prefix="orc_"):
+    lib = lib or orc
+    quat, v = _a(quat), _a(v)
+    out = np.empty_like(v)
+    _call(lib, prefix + "quat_rotate", len(v), quat, v, out)
+    return out
+
+
+def rotate_quaternion(quat, omega, dt, lib=None, prefix="orc_"):
+    lib = lib or orc
+    q = _a(quat).copy()
+    _call(lib, prefix + "rotate_quaternion", len(q), q, _a(omega), float(dt))
+    return q
+
+
+def segseg(l0, l1, m0, m1, lib=None, prefix="orc_"):
+    lib = lib or orc
+    l0, l1, m0, m1 = _a(l0), _a(l1), _a(m0), _a(m1)
+    n = len(l0)
+    dist, s, t = np.empty(n), np.empty(n), np.empty(n)
+    cp1, cp2, sep = np.empty((n, 3)), np.empty((n, 3)), np.empty((n, 3))
+    _call(lib, prefix + "segseg", n, l0, l1, m0, m1, dist, s, t, cp1, cp2, sep)
+    return dist, s, t, cp1, cp2, sep
+
+
+def point_seg(x, p1, p2, lib=None, prefix="orc_"):
+    lib = lib or orc
+    x, p1, p2 = _a(x), _a(p1), _a(p2)
+    n = len(x)
+    dist, t, cp, sep = np.empty(n), np.empty(n), np.empty((n, 3)), np.empty((n, 3))
+    _call(lib, prefix + "point_seg", n, x, p1, p2, dist, t, cp, sep)
+    return dist, t, cp, sep
+
+
+def sphere_sphere(c1, r1, c2, r2, lib=None, prefix="orc_"):
+    lib = lib or orc
+    c1, r1, c2, r2 = _a(c1), _a(r1), _a(c2), _a(r2)
+    n = len(r1)
+    dist, sep = np.empty(n), np.empty((n, 3))
+    _call(lib, prefix + "sphere_sphere", n, c1, r1, c2, r2, dist, sep)
+    return dist, sep
+
+
+def seg_sphere(p1, p2, c, r, lib=None, prefix="orc_"):
+    lib = lib or orc
+    p1, p2, c, r = _a(p1), _a(p2), _a(c), _a(r)
+    n = len(r)
+    dist, t, cp, sep = np.empty(n), np.empty(n), np.empty((n, 3)), np.empty((n, 3))
+    _call(lib, prefix + "seg_sphere", n, p1, p2, c, r, dist, t, cp, sep)
+    return dist, t, cp, sep
+
+
+# ---- collision path (oracle only) -----------------------------------------------------------------------------------
+def search_radii(r, buffer, kind=None, length=None):
+    r = _a(r)
+    S = np.empty(len(r))
+    _call(orc, "orc_search_radii", len(r), _a(kind, _i), r, _a(length), float(buffer), S)
+    return S
+
+
+def search(pos, S, brute=False):
+    pos, S = _a(pos), _a(S)
+    n = len(S)
+    fn = "orc_search_brute" if brute else "orc_search_cells"
+    cap = max(1024, 64 * n)
+    while True:
+        pairs = np.empty((cap, 2), dtype=_i)
+        cnt = _call(orc, fn, n, pos, S, pairs, cap, restype=C.c_long)
+        if cnt <= cap:
+            return pairs[:cnt].copy()
+        cap = cnt
+
+
+def filter_shape_distance(pairs, pos, quat, r, length, kind, cutoff):
+    pairs = _a(pairs, _i)
+    out = np.empty_like(pairs)
+    cnt = _call(orc, "orc_filter_shape_distance", len(pairs), pairs, _a(pos), _a(quat), _a(r), _a(length),
+                _a(kind, _i), float(cutoff), out, restype=C.c_long)
+    return out[:cnt].copy()
+
+
+def moved_too_much(pos, pos_at_build, buffer):
+    return bool(_call(orc, "orc_moved_too_much", len(pos), _a(pos), _a(pos_at_build), float(buffer), restype=C.c_int))
+
+
+def narrow_phase(pairs, pos, r, quat=None, length=None, kind=None, arms=False):
+    pairs = _a(pairs, _i)
+    m = len(pairs)
+    phi, normal = np.empty(m), np.empty((m, 3))
+    ai = np.empty((m, 3)) if arms else None
+    aj = np.empty((m, 3)) if arms else None
+    _call(orc, "orc_narrow_phase", m, pairs, _a(pos), _a(quat), _a(r), _a(length), _a(kind, _i), phi, normal, ai, aj)
+    return phi, normal, ai, aj
+
+
+def apply_D(n, pairs, normal, gamma, arm_i=None, arm_j=None):
+    pairs = _a(pairs, _i)
+    F = np.empty((n, 3))
+    T = np.empty((n, 3)) if arm_i is not None else None
+    _call(orc, "orc_apply_D", n, len(pairs), pairs, _a(normal), _a(arm_i), _a(arm_j), _a(gamma), F, T)
+    return F, T
+
+
+def apply_M(r, mu, F, T=None, quat=None, kind=None):
+    U = np.empty_like(_a(F))
+    W = np.empty_like(U) if T is not None else None
+    _call(orc, "orc_apply_M", len(r), _a(quat), _a(r), _a(kind, _i), float(mu), _a(F), _a(T), U, W)
+    return U, W
+
+
+def apply_DT(n, pairs, normal, U, W=None, arm_i=None, arm_j=None):
+    pairs = _a(pairs, _i)
+    g = np.empty(len(pairs))
+    _call(orc, "orc_apply_DT", n, len(pairs), pairs, _a(normal), _a(arm_i), _a(arm_j), _a(U), _a(W), g)
+    return g
+
+
+def apply_A(n, pairs, normal, r, mu, dt, x, arm_i=None, arm_j=None, quat=None, kind=None):
+    pairs = _a(pairs, _i)
+    y = np.empty(len(pairs))
+    _call(orc, "orc_apply_A", n, len(pairs), pairs, _a(normal), _a(arm_i), _a(arm_j), _a(quat), _a(r), _a(kind, _i),
+          float(mu), float(dt), _a(x), y)
+    return y
+
+
+def resolve_collisions(n, pairs, normal, r, mu, dt, tol, max_it, phi0, gamma0=None, fixed_iters=-1, arm_i=None,
+                       arm_j=None, quat=None, kind=None, U_ext=None, W_ext=None):
+    """Returns dict(res, it, max_disp, gamma, phi0, F, T, U, W). Inputs are not modified."""
+    pairs = _a(pairs, _i)
+    m = len(pairs)
+    phi0 = _a(phi0).copy()
+    gamma = np.zeros(m) if gamma0 is None else _a(gamma0).copy()
+    six = arm_i is not None
+    F, U = np.zeros((n, 3)), np.zeros((n, 3))
+    T = np.zeros((n, 3)) if six else None
+    W = np.zeros((n, 3)) if six else None
+    res = CollisionResult()
+    fn = orc.orc_resolve_collisions
+    fn.restype = None
+    fn(C.c_long(n), C.c_long(m), _p(pairs), _p(_a(normal)), _p(_a(arm_i)), _p(_a(arm_j)), _p(_a(quat)), _p(_a(r)),
+       _p(_a(kind, _i)), C.c_double(mu), C.c_double(dt), C.c_double(tol), C.c_int(max_it), C.c_int(fixed_iters),
+       _p(_a(U_ext)), _p(_a(W_ext)), _p(phi0), _p(gamma), _p(F), _p(T), _p(U), _p(W), C.byref(res))
+    return dict(res=res.max_abs_projected_sep, it=res.ite_count, max_disp=res.max_displacement, gamma=gamma,
+                phi0=phi0, F=F, T=T, U=U, W=W)
+
+
+def euler_update(pos, U, dt, quat=None, kind=None, W=None):
+    pos = _a(pos).copy()
+    q = _a(quat).copy() if quat is not None else None
+    _call(orc, "orc_euler_update", len(pos), pos, q, _a(kind, _i), _a(U), _a(W), float(dt))
+    return pos, q
+
+
+def abc_flow_force(pos):
+    F = np.zeros_like(_a(pos))
+    _call(orc, "orc_abc_flow_force", len(pos), _a(pos), F)
+    return F
+
+
+# ---- math::convex (both libraries) ------------------------------------------------------------------------------------
+def solve_cqpp_dense(A, q, x0, space_kind=1, lo=0.0, hi=0.0, max_iters=1000, tol=1e-8, resid_kind=0, lib=None,
+                     prefix="orc_"):
+    lib = lib or orc
+    A, q = _a(A), _a(q)
+    x = _a(x0).copy()
+    iters, resid = C.c_uint(0), C.c_double(0.0)
+    fn = getattr(lib, prefix + "solve_cqpp_dense")
+    fn.restype = C.c_int
+    conv = fn(C.c_long(len(q)), _p(A), _p(q), _p(x), C.c_int(space_kind), C.c_double(lo), C.c_double(hi),
+              C.c_uint(max_iters), C.c_double(tol), C.c_int(resid_kind), C.byref(iters), C.byref(resid))
+    return dict(x=x, iters=iters.value, residual=resid.value, converged=bool(conv))
+
+
+def solve_contact_lcp_convex(n, pairs, normal, r, mu, dt, phi0, gamma0, max_iters=1000, tol=1e-8, resid_kind=0,
+                             arm_i=None, arm_j=None, quat=None, kind=None):
+    pairs = _a(pairs, _i)
+    keep = [pairs, _a(normal), _a(arm_i), _a(arm_j), _a(quat), _a(r), _a(kind, _i)]
+    ctx = ContactOpCtx(n, len(pairs), *[_p(k) for k in keep], mu, dt)
+    gamma = _a(gamma0).copy()
+    iters, resid = C.c_uint(0), C.c_double(0.0)
+    fn = orc.orc_solve_contact_lcp_convex
+    fn.restype = C.c_int
+    conv = fn(C.byref(ctx), _p(_a(phi0)), _p(gamma), C.c_uint(max_iters), C.c_double(tol), C.c_int(resid_kind),
+              C.byref(iters), C.byref(resid))
+    return dict(x=gamma, iters=iters.value, residual=resid.value, converged=bool(conv))

@@ -1,0 +1,142 @@
+"""GPU parity tests, stage by stage, through the C-ABI (mundy_b200.ops -> libmundy_b200.so) against the CPU oracle.
+
+Bar: bit-exact for index work (pair sets) and for every per-element fp64 stage whose operation order is pinned
+(AABB, distance, narrow phase, D / M / D^T); 1e-10 relative where a reduction order or libm (sin/cos) differs.
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from mundy_b200 import workloads as wl
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [0, 1, 2, 255, 256, 257, 10_000]
+
+
+def dev(x, dtype=torch.float64):
+    return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype, device="cuda")
+
+
+def host(t):
+    return t.detach().cpu().numpy()
+
+
+def rand_quat(rng, n, unit=True):
+    q = rng.normal(size=(n, 4))
+    if unit:
+        q /= np.linalg.norm(q, axis=1, keepdims=True)
+    return q
+
+
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", SIZES)
+def test_aabb_sphere_bit_exact(cuda, n):
+    from mundy_b200 import ops
+    rng = np.random.default_rng(n)
+    c, r = rng.uniform(-50, 50, (n, 3)), rng.uniform(0.1, 2, n)
+    got = host(ops.compute_aabb_sphere(dev(c), dev(r)))
+    assert np.array_equal(got, oracle.aabb_sphere(c, r).reshape(n, 6))
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_aabb_spherocylinder_bit_exact(cuda, n):
+    from mundy_b200 import ops
+    rng = np.random.default_rng(100 + n)
+    c, r, L = rng.uniform(-50, 50, (n, 3)), rng.uniform(0.1, 2, n), rng.uniform(0, 10, n)
+    q = rand_quat(rng, n, unit=False)  # the reference does not assume unit norm
+    got = host(ops.compute_aabb_spherocylinder(dev(c), dev(q), dev(r), dev(L)))
+    assert np.array_equal(got, oracle.aabb_spherocylinder(c, q, r, L).reshape(n, 6))
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_aabb_segment_bit_exact(cuda, n):
+    from mundy_b200 import ops
+    rng = np.random.default_rng(200 + n)
+    a, b, r = rng.uniform(-5, 5, (n, 3)), rng.uniform(-5, 5, (n, 3)), rng.uniform(0.1, 2, n)
+    got = host(ops.compute_aabb_segment(dev(a), dev(b), dev(r)))
+    assert np.array_equal(got, oracle.aabb_segment(a, b, r).reshape(n, 6))
+
+
+def test_aabb_reference_goldens(cuda):
+    """mundy/geom/tests/unit_tests/UnitTestComputeAABB.cpp:180-240 (sphere and spherocylinder cases)."""
+    from mundy_b200 import ops
+    got = host(ops.compute_aabb_sphere(dev([[1.0, -2.0, 3.0]]), dev([2.0])))
+    assert np.allclose(got, [[-1, -4, 1, 3, 0, 5]], atol=1e-12)
+    s = np.sqrt(0.5)
+    q = np.array([[s, s, 0.0, 0.0]])  # 90 degrees about x: z_hat -> -y_hat
+    got = host(ops.compute_aabb_spherocylinder(dev([[1.0, -2.0, 3.0]]), dev(q), dev([2.0]), dev([3.0])))
+    assert np.allclose(got, [[-1, -5.5, 1, 3, 1.5, 5]], atol=1e-12)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def _segments(rng, n):
+    l0, l1 = rng.uniform(-3, 3, (n, 3)), rng.uniform(-3, 3, (n, 3))
+    m0, m1 = rng.uniform(-3, 3, (n, 3)), rng.uniform(-3, 3, (n, 3))
+    k = n // 8
+    if k:
+        m1[:k] = m0[:k] + 1.7 * (l1[:k] - l0[:k])           # parallel -> collinear branch
+        m0[k:2 * k] = l0[k:2 * k]                          # shared endpoint
+        l1[2 * k:3 * k] = l0[2 * k:3 * k]                  # degenerate (zero-length) segment
+        m1[3 * k:4 * k] = m0[3 * k:4 * k] = l0[3 * k:4 * k]  # both degenerate and coincident-ish
+        m1[3 * k:4 * k] += 1e-3
+    return l0, l1, m0, m1
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_distance_segment_segment_bit_exact(cuda, n):
+    from mundy_b200 import ops
+    l0, l1, m0, m1 = _segments(np.random.default_rng(300 + n), n)
+    got = ops.distance_segment_segment(dev(l0), dev(l1), dev(m0), dev(m1))
+    want = oracle.segseg(l0, l1, m0, m1)
+    for g, w in zip(got, want):
+        assert np.array_equal(host(g), w.reshape(host(g).shape))
+
+
+@pytest.mark.parametrize("n", [0, 1, 1000])
+def test_distance_other_pairs_bit_exact(cuda, n):
+    from mundy_b200 import ops
+    rng = np.random.default_rng(400 + n)
+    a, b, c = rng.uniform(-3, 3, (n, 3)), rng.uniform(-3, 3, (n, 3)), rng.uniform(-3, 3, (n, 3))
+    r1, r2 = rng.uniform(0.1, 1, n), rng.uniform(0.1, 1, n)
+    for g, w in zip(ops.distance_sphere_sphere(dev(a), dev(r1), dev(b), dev(r2)), oracle.sphere_sphere(a, r1, b, r2)):
+        assert np.array_equal(host(g), w.reshape(host(g).shape))
+    for g, w in zip(ops.distance_point_segment(dev(a), dev(b), dev(c)), oracle.point_seg(a, b, c)):
+        assert np.array_equal(host(g), w.reshape(host(g).shape))
+    for g, w in zip(ops.distance_segment_sphere(dev(a), dev(b), dev(c), dev(r1)), oracle.seg_sphere(a, b, c, r1)):
+        assert np.array_equal(host(g), w.reshape(host(g).shape))
+
+
+def test_segment_segment_reference_golden(cuda):
+    """The 'pesky' collinear case of mundy/geom/tests/unit_tests/UnitTestSegmentSegment.cpp:459-468."""
+    from mundy_b200 import ops
+    golden = np.load(__import__("os").path.join(__import__("os").path.dirname(__file__), "golden", "segseg_cases.npz"))
+    got = ops.distance_segment_segment(dev(golden["l0"]), dev(golden["l1"]), dev(golden["m0"]), dev(golden["m1"]))
+    assert np.allclose(host(got[0]), golden["dist"], rtol=0, atol=1e-12)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def _bodies_dev(w):
+    from mundy_b200 import ops
+    t = dict(center=dev(w["center"]), radius=dev(w["radius"]))
+    if "kind" in w:
+        t.update(quat=dev(w["quat"]), length=dev(w["length"]), kind=dev(w["kind"], torch.int32))
+    return ops.make_bodies(t["center"], t["radius"], t.get("quat"), t.get("length"), t.get("kind")), t
+
+
+@pytest.mark.parametrize("maker,kw", [(wl.monodisperse_spheres, dict(n=3000)), (wl.polydisperse_spheres, dict(n=3000)),
+                                      (wl.rods, dict(n=2000, phi=0.2)), (wl.mixed, dict(n=2000))])
+def test_narrow_phase_bit_exact(cuda, maker, kw):
+    from mundy_b200 import ops
+    w = maker(**kw)
+    S = oracle.search_radii(w["radius"], 0.3, w.get("kind"), w.get("length"))
+    pairs = oracle.search(w["center"], S)
+    assert len(pairs) > 100
+    arms = "kind" in w
+    want = oracle.narrow_phase(pairs, w["center"], w["radius"], w.get("quat"), w.get("length"), w.get("kind"), arms)
+    bodies, _ = _bodies_dev(w)
+    got = ops.narrow_phase(bodies, dev(pairs, torch.int32), arms=arms)
+    for g, x in zip(got, want):
+        if x is not None:
+            assert np.array_equal(host(g), x.reshape(host(g).shape))
