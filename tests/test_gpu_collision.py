@@ -1,0 +1,219 @@
+"""GPU parity tests of the collision path proper: broad phase, contact operator, BBPGD, math::convex, Euler, whole step.
+Everything goes through the C-ABI (mundy_b200.ops) and is compared with the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from mundy_b200 import workloads as wl
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-10  # north_star: fp64 values within 1e-10 relative
+
+
+def dev(x, dtype=torch.float64):
+    return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype, device="cuda")
+
+
+def host(t):
+    return t.detach().cpu().numpy()
+
+
+def rel(a, b):
+    scale = max(np.max(np.abs(b)), 1e-300)
+    return np.max(np.abs(a - b)) / scale
+
+
+def bodies_of(w):
+    from mundy_b200 import ops
+    t = dict(center=dev(w["center"]), radius=dev(w["radius"]))
+    if "kind" in w:
+        t.update(quat=dev(w["quat"]), length=dev(w["length"]), kind=dev(w["kind"], torch.int32))
+    return ops.make_bodies(t["center"], t["radius"], t.get("quat"), t.get("length"), t.get("kind")), t
+
+
+# ---- broad phase ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,edge,seed", [(1, 1.0, 0), (2, 1.0, 1), (50, 3.0, 2), (3000, 30.0, 3), (20000, 60.0, 4)])
+def test_search_pairs_bit_exact(cuda, n, edge, seed):
+    from mundy_b200 import ops
+    rng = np.random.default_rng(seed)
+    pos = rng.uniform(0, edge, (n, 3))
+    S = rng.uniform(0.5, 2.0, n)
+    want = oracle.search(pos, S, brute=n <= 3000)
+    got = host(ops.search_pairs(dev(pos), dev(S)))
+    assert got.shape == want.shape and np.array_equal(got, want)
+
+
+def test_search_pairs_degenerate_inputs(cuda):
+    from mundy_b200 import ops
+    # all bodies at the same point: every pair is a candidate
+    pos = np.zeros((40, 3))
+    got = host(ops.search_pairs(dev(pos), dev(np.ones(40))))
+    assert len(got) == 40 * 39 // 2 and np.array_equal(got, oracle.search(pos, np.ones(40), brute=True))
+    # zero search radii, distinct points: no pairs; coincident points with zero radius touch (<=)
+    pos = np.array([[0.0, 0, 0], [1, 0, 0], [1, 0, 0]])
+    assert host(ops.search_pairs(dev(pos), dev(np.zeros(3)))).tolist() == [[1, 2]]
+    # exactly touching search spheres count (closed predicate, AABB.hpp:419-431 "touching counts")
+    pos = np.array([[0.0, 0, 0], [2.0, 0, 0]])
+    assert host(ops.search_pairs(dev(pos), dev(np.ones(2)))).tolist() == [[0, 1]]
+    # a very elongated cloud (cell table limits force larger cells)
+    rng = np.random.default_rng(9)
+    pos = rng.uniform(0, 1, (5000, 3)) * np.array([5000.0, 2.0, 2.0])
+    S = np.full(5000, 0.6)
+    assert np.array_equal(host(ops.search_pairs(dev(pos), dev(S))), oracle.search(pos, S))
+
+
+def test_two_overlapping_spheres_one_link(cuda):
+    """mundy/mesh/tests/unit_tests/UnitTestGenNeighborLinks.cpp:73-152."""
+    from mundy_b200 import ops
+    w = dict(center=np.array([[0.0, 0, 0], [1.0, 0, 0], [10.0, 0, 0]]), radius=np.ones(3))
+    b, _ = bodies_of(w)
+    links = ops.NeighborLinks().set_search_buffer(0.0)
+    assert links.generate(b) and links.count() == 1 and host(links.pairs()).tolist() == [[0, 1]]
+
+
+@pytest.mark.parametrize("maker,kw,buffer", [(wl.polydisperse_spheres, dict(n=20000), 0.25),
+                                             (wl.rods, dict(n=8000, phi=0.15), 0.5), (wl.mixed, dict(n=6000), 0.3)])
+def test_neighbor_links_candidates_and_filter(cuda, maker, kw, buffer):
+    from mundy_b200 import ops
+    w = maker(**kw)
+    S = oracle.search_radii(w["radius"], buffer, w.get("kind"), w.get("length"))
+    want = oracle.search(w["center"], S)
+    b, _ = bodies_of(w)
+    links = ops.NeighborLinks().set_search_buffer(buffer)
+    assert links.generate(b)
+    assert np.array_equal(host(links.pairs()), want)
+    if "kind" in w:
+        links.set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
+        assert links.generate(b)  # changing the filter invalidates the list
+        kept = oracle.filter_shape_distance(want, w["center"], w["quat"], w["radius"], w["length"], w["kind"], 2 * buffer)
+        assert 0 < len(kept) < len(want)
+        assert np.array_equal(host(links.pairs()), kept)
+
+
+def test_rebuild_trigger(cuda):
+    """generate() returns false until some body moved more than half the buffer (GenNeighborLinkers.hpp:603-615)."""
+    from mundy_b200 import ops
+    w = wl.monodisperse_spheres(2000)
+    b, t = bodies_of(w)
+    links = ops.NeighborLinks().set_search_buffer(1.0)
+    assert links.generate(b) is True
+    assert links.generate(b) is False
+    t["center"][17, 0] += 0.499
+    assert links.generate(b) is False
+    assert not oracle.moved_too_much(host(t["center"]), w["center"], 1.0)
+    t["center"][17, 0] += 0.002
+    assert oracle.moved_too_much(host(t["center"]), w["center"], 1.0)
+    assert links.generate(b) is True
+    assert links.generate(b) is False and links.generate(b, force=True) is True
+
+
+# ---- contact operator ---------------------------------------------------------------------------------------------
+def contact_system(w, buffer):
+    S = oracle.search_radii(w["radius"], buffer, w.get("kind"), w.get("length"))
+    pairs = oracle.search(w["center"], S)
+    arms = "kind" in w
+    phi, nrm, ai, aj = oracle.narrow_phase(pairs, w["center"], w["radius"], w.get("quat"), w.get("length"),
+                                           w.get("kind"), arms)
+    return pairs, phi, nrm, ai, aj
+
+
+def gpu_op(w, pairs, nrm, ai, aj, mu, dt):
+    from mundy_b200 import ops
+    return ops.make_contact_op(len(w["radius"]), dev(pairs, torch.int32), dev(nrm), dev(w["radius"]), mu, dt,
+                               dev(ai) if ai is not None else None, dev(aj) if aj is not None else None,
+                               dev(w["quat"]) if "quat" in w else None,
+                               dev(w["kind"], torch.int32) if "kind" in w else None)
+
+
+@pytest.mark.parametrize("maker,kw", [(wl.polydisperse_spheres, dict(n=4000)), (wl.rods, dict(n=3000, phi=0.2)),
+                                      (wl.mixed, dict(n=3000))])
+def test_operator_pieces_bit_exact(cuda, maker, kw):
+    from mundy_b200 import ops
+    w = maker(**kw)
+    n = len(w["radius"])
+    pairs, phi, nrm, ai, aj = contact_system(w, 0.3)
+    rng = np.random.default_rng(5)
+    gamma = rng.uniform(0, 1, len(pairs))
+    mu, dt = 1e-3, 1e-2
+    op = gpu_op(w, pairs, nrm, ai, aj, mu, dt)
+    F, T = ops.apply_D(op, dev(gamma))
+    Fo, To = oracle.apply_D(n, pairs, nrm, gamma, ai, aj)
+    assert np.array_equal(host(F), Fo) and (To is None or np.array_equal(host(T), To))
+    U, W = ops.apply_M(op, F, T)
+    Uo, Wo = oracle.apply_M(w["radius"], mu, Fo, To, w.get("quat"), w.get("kind"))
+    assert np.array_equal(host(U), Uo) and (Wo is None or np.array_equal(host(W), Wo))
+    g = ops.apply_DT(op, U, W)
+    go = oracle.apply_DT(n, pairs, nrm, Uo, Wo, ai, aj)
+    assert np.array_equal(host(g), go)
+    y = ops.apply_A(op, dev(gamma))
+    yo = oracle.apply_A(n, pairs, nrm, w["radius"], mu, dt, gamma, ai, aj, w.get("quat"), w.get("kind"))
+    assert np.array_equal(host(y), yo)
+
+
+# ---- BBPGD --------------------------------------------------------------------------------------------------------
+CASES = [("cfg1_spheres", wl.monodisperse_spheres, dict(n=10000), 3.0, dict(mu=1e-3, dt=5e-3, tol=1e-5)),
+         ("poly_spheres", wl.polydisperse_spheres, dict(n=6000, phi=0.2), 0.5, dict(mu=1e-3, dt=1e-2, tol=1e-5)),
+         ("rods", wl.rods, dict(n=4000, phi=0.1, length=4.0), 0.5, dict(mu=1e-3, dt=1e-2, tol=1e-5)),
+         ("mixed", wl.mixed, dict(n=4000, phi=0.2), 0.4, dict(mu=1e-3, dt=1e-2, tol=1e-5))]
+
+
+@pytest.mark.parametrize("name,maker,kw,buffer,p", CASES, ids=[c[0] for c in CASES])
+@pytest.mark.parametrize("iters", [0, 1, 2, 5, 12])
+def test_bbpgd_fixed_iterations(cuda, name, maker, kw, buffer, p, iters):
+    """gamma_K, forces and velocities after exactly K iterations match the oracle to 1e-10 relative."""
+    from mundy_b200 import ops
+    w = maker(**kw)
+    n = len(w["radius"])
+    pairs, phi, nrm, ai, aj = contact_system(w, buffer)
+    want = oracle.resolve_collisions(n, pairs, nrm, w["radius"], p["mu"], p["dt"], p["tol"], 10000, phi,
+                                     fixed_iters=iters, arm_i=ai, arm_j=aj, quat=w.get("quat"), kind=w.get("kind"))
+    op = gpu_op(w, pairs, nrm, ai, aj, p["mu"], p["dt"])
+    phi_d, gam_d = dev(phi), torch.zeros(len(pairs), dtype=torch.float64, device="cuda")
+    res, F, T, U, W = ops.resolve_collisions(op, phi_d, gam_d, p["tol"], 10000, fixed_iters=iters)
+    assert res.ite_count == want["it"] == iters
+    assert abs(res.max_abs_projected_sep - want["res"]) <= RTOL * abs(want["res"])
+    assert rel(host(gam_d), want["gamma"]) <= RTOL or np.max(np.abs(want["gamma"])) == 0
+    assert rel(host(F), want["F"]) <= RTOL or iters == 0
+    assert rel(host(U), want["U"]) <= RTOL or iters == 0
+    if ai is not None and iters > 0:
+        assert rel(host(T), want["T"]) <= RTOL and rel(host(W), want["W"]) <= RTOL
+    assert abs(res.max_displacement - want["max_disp"]) <= RTOL * max(want["max_disp"], 1e-300) or iters == 0
+
+
+@pytest.mark.parametrize("name,maker,kw,buffer,p", CASES, ids=[c[0] for c in CASES])
+def test_bbpgd_converged(cuda, name, maker, kw, buffer, p):
+    """Run to the reference's tolerance: same iteration count, residual below tol, and the converged contact forces
+    and velocities agree with the oracle (1e-10 when the iteration counts agree, which they must here)."""
+    from mundy_b200 import ops
+    w = maker(**kw)
+    n = len(w["radius"])
+    pairs, phi, nrm, ai, aj = contact_system(w, buffer)
+    want = oracle.resolve_collisions(n, pairs, nrm, w["radius"], p["mu"], p["dt"], p["tol"], 10000, phi, arm_i=ai,
+                                     arm_j=aj, quat=w.get("quat"), kind=w.get("kind"))
+    op = gpu_op(w, pairs, nrm, ai, aj, p["mu"], p["dt"])
+    phi_d, gam_d = dev(phi), torch.zeros(len(pairs), dtype=torch.float64, device="cuda")
+    res, F, T, U, W = ops.resolve_collisions(op, phi_d, gam_d, p["tol"], 10000)
+    assert res.converged and res.max_abs_projected_sep < p["tol"] and want["res"] < p["tol"]
+    assert res.ite_count == want["it"], (res.ite_count, want["it"])
+    # post-solve relative agreement; 1e-8 leaves room for the rounding-order amplification over ~100 BB iterations
+    assert rel(host(gam_d), want["gamma"]) <= 1e-8
+    assert rel(host(F), want["F"]) <= 1e-8 and rel(host(U), want["U"]) <= 1e-8
+    print(name, "iters", res.ite_count, "rel gamma", rel(host(gam_d), want["gamma"]), "rel U", rel(host(U), want["U"]))
+
+
+def test_bbpgd_external_velocity_and_warm_start(cuda):
+    from mundy_b200 import ops
+    w = wl.polydisperse_spheres(5000, phi=0.2)
+    n = len(w["radius"])
+    pairs, phi, nrm, ai, aj = contact_system(w, 0.5)
+    mu, dt, tol = 1e-3, 1e-2, 1e-5
+    Uext = oracle.apply_M(w["radius"], mu, oracle.abc_flow_force(w["center"]))[0]
+    g0 = np.random.default_rng(1).uniform(0, 0.1, len(pairs))
+    want = oracle.resolve_collisions(n, pairs, nrm, w["radius"], mu, dt, tol, 10000, phi, gamma0=g0, fixed_iters=6,
+                                     U_ext=Uext)
+    op = gpu_op(w, pairs, nrm, ai, aj, mu, dt)
+    phi_d, gam_d = dev(phi), dev(g0)
+    res, F, T, U, W = ops.resolve_collisions(op, phi_d, gam_d, tol, 10000, fixed_iters=6, U_ext=dev(Uext))
+    assert np.array_equal(host(phi_d), want["phi0"])  # corrected in place, bit-exact
+    assert rel(host(gam_d), want["gamma"]) <= RTOL and rel(host(U), want["U"]) <= RTOL
