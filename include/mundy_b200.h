@@ -243,6 +243,11 @@ int mb200_solve_lcp_contact(mb200_stream stream, const mb200_contact_op* op, con
 int mb200_euler_update(mb200_stream stream, int64_t n, double* center, double* quat, const int32_t* kind,
                        const double* U, const double* W, double dt);
 
+/* External forcing of the multi-step driver: the "attractive ABC flow"
+ * F += (a sin z + c cos y, b sin x + a cos z, c sin y + b cos x) - 2 x/|x|, a = 1, b = sqrt 2, c = sqrt 3
+ * (scrap/parameter_interface/NGPSpheresLCP.cpp:971-998). center[3n] in, F[3n] in/out (accumulated into). */
+int mb200_abc_flow_force(mb200_stream stream, int64_t n, const double* center, double* F);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Whole collision timestep (the loop body of scrap/parameter_interface/NGPSpheresLCP.cpp:1135-1292):
  *   generate links if needed -> narrow phase -> (phi0 += dt D^T U_ext) -> BBPGD -> U += U_ext -> Euler.
@@ -281,6 +286,27 @@ int mb200_collision_step_host(mb200_neighbor_links* links, mb200_stream stream, 
 
 /* Total kernels launched by this library in the calling process (a monotone counter; for bench accounting). */
 int64_t mb200_kernel_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Stage timers (the reference drivers print Kokkos::Timer wall times per phase, scrap/lcp_spheres/NGPSpheresLCP.cpp:
+ * 999-1053; here: CUDA events recorded on the stream the kernels are launched on). Off by default; while enabled every
+ * launch of the listed stages is bracketed by an event pair. mb200_profile_read synchronises the recorded events,
+ * returns the accumulated device time [ms] and the number of bracketed regions of one stage since the last
+ * mb200_profile_enable(1), and keeps accumulating.
+ * ------------------------------------------------------------------------------------------------------------- */
+enum mb200_stage {
+  MB200_STAGE_TRIGGER = 0,    /* rebuild trigger (moved more than buffer/2)        one region per step   */
+  MB200_STAGE_BROADPHASE = 1, /* link rebuild: keys, sort, cell table, pair search, incidence lists      */
+  MB200_STAGE_PACK = 2,       /* bodies -> Morton-order records and solver inputs   one region per step   */
+  MB200_STAGE_NARROW = 3,     /* narrow phase                                        one region per step   */
+  MB200_STAGE_LCP_GAMMA = 4,  /* BBPGD: gamma update                                 one region per launch */
+  MB200_STAGE_LCP_BODY = 5,   /* BBPGD: F = D gamma, U = M F                         one region per launch */
+  MB200_STAGE_LCP_RATE = 6,   /* BBPGD: g = D^T U, residual, BB dots                 one region per launch */
+  MB200_STAGE_EULER = 7,      /* velocity totals, Euler update, scatter to the caller's order            */
+  MB200_STAGE_COUNT = 8
+};
+int mb200_profile_enable(int on);
+int mb200_profile_read(int stage, double* ms_total_h, int64_t* regions_h);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -70,6 +70,8 @@ SIGNATURES = {
     "mb200_last_error_string": (C.c_char_p, []),
     "mb200_device_count": (C.c_int, []),
     "mb200_kernel_launch_count": (c_i64, []),
+    "mb200_profile_enable": (C.c_int, [C.c_int]),
+    "mb200_profile_read": (C.c_int, [C.c_int, P(c_dbl), P(c_i64)]),
     "mb200_compute_aabb_sphere": (C.c_int, [vp, c_i64, vp, vp, vp]),
     "mb200_compute_aabb_spherocylinder": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp]),
     "mb200_compute_aabb_segment": (C.c_int, [vp, c_i64, vp, vp, vp, vp]),
@@ -101,6 +103,7 @@ SIGNATURES = {
     "mb200_solve_cqpp_dense": (C.c_int, [vp, c_i64, vp, vp, vp, P(PgdConfig), P(SolveResult)]),
     "mb200_solve_lcp_contact": (C.c_int, [vp, P(ContactOp), vp, vp, P(PgdConfig), P(SolveResult)]),
     "mb200_euler_update": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, c_dbl]),
+    "mb200_abc_flow_force": (C.c_int, [vp, c_i64, vp, vp]),
     "mb200_collision_step": (C.c_int, [vp, vp, P(Bodies), P(StepParams), vp, vp, vp, vp, vp, vp, P(StepStats)]),
     "mb200_collision_step_host": (C.c_int, [vp, vp, P(Bodies), P(StepParams), vp, vp, vp, vp, vp, vp, P(StepStats)]),
 }

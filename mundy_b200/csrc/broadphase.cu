@@ -361,6 +361,7 @@ int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies*
   bool rebuild = force || !h->built || h->n != b->n;
   if (!rebuild && b->n > 0) {
     MB200_TRY(h->flag.reserve(1));
+    StageScope ps(MB200_STAGE_TRIGGER, st);
     MB200_CUDA(cudaMemsetAsync(h->flag.p, 0, sizeof(int32_t), st));
     const bool shape = h->filter == MB200_FILTER_SHAPE_DISTANCE && h->rods;
     moved_kernel<<<grid_for(b->n, 256), 256, 0, st>>>(b->n, b->center, h->ref_center.p, b->quat, b->length, b->kind,
@@ -371,7 +372,10 @@ int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies*
     MB200_CUDA(cudaStreamSynchronize(st));
     rebuild = moved != 0;
   }
-  if (rebuild) MB200_TRY(build_links(st, h, b, nullptr));
+  if (rebuild) {
+    StageScope ps(MB200_STAGE_BROADPHASE, st);
+    MB200_TRY(build_links(st, h, b, nullptr));
+  }
   if (rebuilt_h) *rebuilt_h = rebuild ? 1 : 0;
   return MB200_OK;
 }

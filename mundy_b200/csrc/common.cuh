@@ -55,6 +55,24 @@ inline void count_launch(int k = 1) { g_launches.fetch_add(k, std::memory_order_
 
 inline cudaStream_t as_stream(mb200_stream s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// Stage timers (core.cu). A StageScope brackets the launches issued during its lifetime with an event pair on `st`
+// when profiling is enabled, and costs one relaxed load otherwise.
+extern std::atomic<int> g_profile_on;
+int prof_begin(int stage, cudaStream_t st);
+void prof_end(int idx, cudaStream_t st);
+struct StageScope {
+  int idx = -1;
+  cudaStream_t st;
+  StageScope(int stage, cudaStream_t s) : st(s) {
+    if (g_profile_on.load(std::memory_order_relaxed)) idx = prof_begin(stage, s);
+  }
+  ~StageScope() {
+    if (idx >= 0) prof_end(idx, st);
+  }
+  StageScope(const StageScope&) = delete;
+  StageScope& operator=(const StageScope&) = delete;
+};
+
 // Verifies that a device exists before the first compute call (no CPU fallback).
 int require_device();
 

@@ -1,7 +1,64 @@
 // Library-wide plumbing: error string, launch counter, device check.
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
 
 namespace mb200 {
+
+// ---- stage timers ------------------------------------------------------------------------------------------------
+std::atomic<int> g_profile_on{0};
+namespace {
+struct ProfRegion {
+  int stage;
+  cudaEvent_t a, b;
+  bool closed;
+};
+std::mutex g_prof_mu;
+std::vector<ProfRegion> g_prof_open;       // recorded, not yet folded into the totals
+std::vector<cudaEvent_t> g_prof_free;      // recycled events
+double g_prof_ms[MB200_STAGE_COUNT];
+long long g_prof_regions[MB200_STAGE_COUNT];
+
+cudaEvent_t prof_event() {
+  if (!g_prof_free.empty()) {
+    cudaEvent_t e = g_prof_free.back();
+    g_prof_free.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+void prof_fold() {  // g_prof_mu held
+  for (ProfRegion& r : g_prof_open) {
+    if (!r.closed) continue;
+    float ms = 0.f;
+    if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+      g_prof_ms[r.stage] += ms;
+      g_prof_regions[r.stage] += 1;
+    }
+    g_prof_free.push_back(r.a);
+    g_prof_free.push_back(r.b);
+  }
+  g_prof_open.clear();
+}
+}  // namespace
+
+int prof_begin(int stage, cudaStream_t st) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ProfRegion r{stage, prof_event(), prof_event(), false};
+  if (!r.a || !r.b) return -1;
+  cudaEventRecord(r.a, st);
+  g_prof_open.push_back(r);
+  return static_cast<int>(g_prof_open.size()) - 1;
+}
+void prof_end(int idx, cudaStream_t st) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (idx < 0 || idx >= static_cast<int>(g_prof_open.size())) return;
+  cudaEventRecord(g_prof_open[idx].b, st);
+  g_prof_open[idx].closed = true;
+}
 
 static thread_local std::string t_error;
 std::atomic<long long> g_launches{0};
@@ -48,5 +105,24 @@ int mb200_device_count(void) {
 }
 
 int64_t mb200_kernel_launch_count(void) { return mb200::g_launches.load(std::memory_order_relaxed); }
+
+int mb200_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(mb200::g_prof_mu);
+  mb200::prof_fold();
+  if (on) {
+    for (int k = 0; k < MB200_STAGE_COUNT; ++k) mb200::g_prof_ms[k] = 0.0, mb200::g_prof_regions[k] = 0;
+  }
+  mb200::g_profile_on.store(on ? 1 : 0);
+  return MB200_OK;
+}
+
+int mb200_profile_read(int stage, double* ms_total_h, int64_t* regions_h) {
+  MB200_REQUIRE(stage >= 0 && stage < MB200_STAGE_COUNT && ms_total_h && regions_h, "bad stage or null output");
+  std::lock_guard<std::mutex> lk(mb200::g_prof_mu);
+  mb200::prof_fold();
+  *ms_total_h = mb200::g_prof_ms[stage];
+  *regions_h = mb200::g_prof_regions[stage];
+  return MB200_OK;
+}
 
 }  // extern "C"

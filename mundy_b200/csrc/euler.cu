@@ -25,6 +25,22 @@ __global__ void __launch_bounds__(256) euler_quat_kernel(int64_t n, double* __re
   o[1] = make_double2(q.y, q.z);
 }
 
+// "Attractive ABC flow" forcing of the multi-step driver, F += ... (scrap/parameter_interface/NGPSpheresLCP.cpp:971-998).
+__global__ void __launch_bounds__(256) abc_flow_kernel(int64_t n, const double* __restrict__ center,
+                                                       double* __restrict__ F) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double a = 1.0, b = sqrt(2.0), c = sqrt(3.0), k = 2.0;
+  const V3 p = ld3(center, i);
+  const double rr = sqrt(p.x * p.x + p.y * p.y + p.z * p.z);
+  const double inv_r = 1.0 / rr;
+  V3 f = ld3(F, i);
+  f.x += a * sin(p.z) + c * cos(p.y) - k * p.x * inv_r;
+  f.y += b * sin(p.x) + a * cos(p.z) - k * p.y * inv_r;
+  f.z += c * sin(p.y) + b * cos(p.x) - k * p.z * inv_r;
+  st3(F, i, f);
+}
+
 }  // namespace
 
 int euler_update(cudaStream_t st, int64_t n, double* center, double* quat, const int32_t* kind, const double* U,
@@ -48,4 +64,13 @@ extern "C" int mb200_euler_update(mb200_stream stream, int64_t n, double* center
   MB200_REQUIRE(n >= 0 && (n == 0 || (center && U)), "bad arguments");
   MB200_TRY(require_device());
   return euler_update(as_stream(stream), n, center, quat, kind, U, W, dt);
+}
+
+extern "C" int mb200_abc_flow_force(mb200_stream stream, int64_t n, const double* center, double* F) {
+  MB200_REQUIRE(n >= 0 && (n == 0 || (center && F)), "bad arguments");
+  MB200_TRY(require_device());
+  if (n == 0) return MB200_OK;
+  abc_flow_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(n, center, F);
+  MB200_LAUNCHED();
+  return MB200_OK;
 }

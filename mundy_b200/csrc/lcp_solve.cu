@@ -306,16 +306,22 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
   }
 
   // initial residual: g_a = D^T M D gamma_0
-  if (six) {
-    body_pass_kernel<true, false><<<body_grid, 128, 0, st>>>(a, gamma, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+  {
+    StageScope ps(MB200_STAGE_LCP_BODY, st);
+    if (six)
+      body_pass_kernel<true, false><<<body_grid, 128, 0, st>>>(a, gamma, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+    else
+      body_pass_kernel<false, false><<<body_grid, 128, 0, st>>>(a, gamma, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
     MB200_LAUNCHED();
-    rate_pass_kernel<true, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, gamma, nullptr, nullptr, g_a.p);
-  } else {
-    body_pass_kernel<false, false><<<body_grid, 128, 0, st>>>(a, gamma, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
-    MB200_LAUNCHED();
-    rate_pass_kernel<false, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, gamma, nullptr, nullptr, g_a.p);
   }
-  MB200_LAUNCHED();
+  {
+    StageScope ps(MB200_STAGE_LCP_RATE, st);
+    if (six)
+      rate_pass_kernel<true, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, gamma, nullptr, nullptr, g_a.p);
+    else
+      rate_pass_kernel<false, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, gamma, nullptr, nullptr, g_a.p);
+    MB200_LAUNCHED();
+  }
 
   // iteration it: gamma_cur/g_cur are the B buffers when it is odd, the A buffers when even
   int it = 0;
@@ -334,18 +340,27 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
       const double* gam_prev = odd ? gamma : gamma_b.p;
       double* g_cur = odd ? g_b.p : g_a.p;
       const double* g_prev = odd ? g_a.p : g_b.p;
-      gamma_update_kernel<<<gam_grid, 256, 0, st>>>(C, gam_prev, phi0, g_prev, it == 1 ? 1 : 0, a.dt, state.p, gam_cur);
-      MB200_LAUNCHED();
-      if (six) {
-        body_pass_kernel<true, false><<<body_grid, 128, 0, st>>>(a, gam_cur, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+      {
+        StageScope ps(MB200_STAGE_LCP_GAMMA, st);
+        gamma_update_kernel<<<gam_grid, 256, 0, st>>>(C, gam_prev, phi0, g_prev, it == 1 ? 1 : 0, a.dt, state.p, gam_cur);
         MB200_LAUNCHED();
-        rate_pass_kernel<true, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, gam_cur, gam_prev, g_prev, g_cur);
-      } else {
-        body_pass_kernel<false, false><<<body_grid, 128, 0, st>>>(a, gam_cur, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
-        MB200_LAUNCHED();
-        rate_pass_kernel<false, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, gam_cur, gam_prev, g_prev, g_cur);
       }
-      MB200_LAUNCHED();
+      {
+        StageScope ps(MB200_STAGE_LCP_BODY, st);
+        if (six)
+          body_pass_kernel<true, false><<<body_grid, 128, 0, st>>>(a, gam_cur, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+        else
+          body_pass_kernel<false, false><<<body_grid, 128, 0, st>>>(a, gam_cur, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+        MB200_LAUNCHED();
+      }
+      {
+        StageScope ps(MB200_STAGE_LCP_RATE, st);
+        if (six)
+          rate_pass_kernel<true, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, gam_cur, gam_prev, g_prev, g_cur);
+        else
+          rate_pass_kernel<false, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, gam_cur, gam_prev, g_prev, g_cur);
+        MB200_LAUNCHED();
+      }
     }
     if (batch < 32) batch *= 2;
   }
@@ -353,11 +368,14 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
   // final gamma lives in the B buffer when the last executed iteration is odd
   const int it_final = hs.it;
   if (it_final & 1) MB200_CUDA(cudaMemcpyAsync(gamma, gamma_b.p, C * sizeof(double), cudaMemcpyDeviceToDevice, st));
-  if (six)
-    body_pass_kernel<true, true><<<body_grid, 128, 0, st>>>(a, gamma, F, T, U, W, nullptr, nullptr);
-  else
-    body_pass_kernel<false, true><<<body_grid, 128, 0, st>>>(a, gamma, F, nullptr, U, nullptr, nullptr, nullptr);
-  MB200_LAUNCHED();
+  {
+    StageScope ps(MB200_STAGE_LCP_BODY, st);
+    if (six)
+      body_pass_kernel<true, true><<<body_grid, 128, 0, st>>>(a, gamma, F, T, U, W, nullptr, nullptr);
+    else
+      body_pass_kernel<false, true><<<body_grid, 128, 0, st>>>(a, gamma, F, nullptr, U, nullptr, nullptr, nullptr);
+    MB200_LAUNCHED();
+  }
   MB200_CUDA(cudaMemcpyAsync(pinned.h, state.p, sizeof(LcpState), cudaMemcpyDeviceToHost, st));
   MB200_CUDA(cudaStreamSynchronize(st));
   hs = *pinned.h;

@@ -184,7 +184,6 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
     // bodies -> Morton-order records and solver parameters
     MB200_TRY(h->b0.reserve(n));
     if (rods) MB200_TRY(h->b1.reserve(n));
-    MB200_TRY(pack_bodies(st, bodies, reinterpret_cast<const int32_t*>(h->perm.p), h->b0.p, rods ? h->b1.p : nullptr));
     MB200_TRY(h->radius_s.reserve(n));
     if (rods) {
       MB200_TRY(h->quat_s.reserve(4 * n));
@@ -200,12 +199,6 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
         Wext_s = h->vec_b.p;
       }
     }
-    gather_params_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, bodies->radius, bodies->quat, bodies->kind,
-                                                          params->viscosity, F_ext, T_ext, h->radius_s.p,
-                                                          rods ? h->quat_s.p : nullptr, rods ? h->kind_s.p : nullptr,
-                                                          Uext_s, Wext_s);
-    MB200_LAUNCHED();
-    // narrow phase on the links
     MB200_TRY(h->phi0.reserve(C + 1));
     MB200_TRY(h->normal.reserve(3 * C + 1));
     MB200_TRY(h->gamma.reserve(C + 1));
@@ -213,8 +206,20 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
       MB200_TRY(h->arm_i.reserve(3 * C + 1));
       MB200_TRY(h->arm_j.reserve(3 * C + 1));
     }
-    MB200_TRY(narrow_phase_records(st, C, h->pairs.p, h->b0.p, rods ? h->b1.p : nullptr, h->phi0.p, h->normal.p,
-                                   rods ? h->arm_i.p : nullptr, rods ? h->arm_j.p : nullptr));
+    {
+      StageScope ps(MB200_STAGE_PACK, st);
+      MB200_TRY(pack_bodies(st, bodies, reinterpret_cast<const int32_t*>(h->perm.p), h->b0.p, rods ? h->b1.p : nullptr));
+      gather_params_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, bodies->radius, bodies->quat, bodies->kind,
+                                                            params->viscosity, F_ext, T_ext, h->radius_s.p,
+                                                            rods ? h->quat_s.p : nullptr, rods ? h->kind_s.p : nullptr,
+                                                            Uext_s, Wext_s);
+      MB200_LAUNCHED();
+    }
+    {  // narrow phase on the links
+      StageScope ps(MB200_STAGE_NARROW, st);
+      MB200_TRY(narrow_phase_records(st, C, h->pairs.p, h->b0.p, rods ? h->b1.p : nullptr, h->phi0.p, h->normal.p,
+                                     rods ? h->arm_i.p : nullptr, rods ? h->arm_j.p : nullptr));
+    }
     // LCP
     MB200_TRY(h->vec_c.reserve(3 * n));
     MB200_TRY(h->vec_d.reserve(3 * n));
@@ -240,10 +245,13 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
       if (stats_h) *stats_h = mb200_step_stats{res, C, rebuilt, static_cast<int32_t>(g_launches.load() - launches0)};
       return MB200_ERR_NOT_CONVERGED;
     }
-    scatter_euler_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, params->dt, F_s, T_s, U_s, W_s, Uext_s, Wext_s,
-                                                          bodies->kind, bodies->center, bodies->quat, F_col, T_col,
-                                                          U_out, W_out);
-    MB200_LAUNCHED();
+    {
+      StageScope ps(MB200_STAGE_EULER, st);
+      scatter_euler_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, params->dt, F_s, T_s, U_s, W_s, Uext_s,
+                                                            Wext_s, bodies->kind, bodies->center, bodies->quat, F_col,
+                                                            T_col, U_out, W_out);
+      MB200_LAUNCHED();
+    }
   }
   MB200_CUDA(cudaStreamSynchronize(st));
   if (stats_h) *stats_h = mb200_step_stats{res, C, rebuilt, static_cast<int32_t>(g_launches.load() - launches0)};

@@ -264,5 +264,28 @@ def euler_update(center, U, dt, quat=None, kind=None, W=None):
                                  dt), "euler_update")
 
 
+def abc_flow_force(center, F):
+    """F += attractive ABC flow force at `center` (in place)."""
+    check(lib.mb200_abc_flow_force(_stream(), center.shape[0], _f64(center), _f64(F)), "abc_flow_force")
+    return F
+
+
 def kernel_launch_count():
     return lib.mb200_kernel_launch_count()
+
+
+STAGES = ("trigger", "broadphase", "pack", "narrow", "lcp_gamma", "lcp_body", "lcp_rate", "euler")
+
+
+def profile_enable(on=True):
+    check(lib.mb200_profile_enable(int(bool(on))), "profile_enable")
+
+
+def profile_read():
+    """{stage: (device ms accumulated since profile_enable(True), number of bracketed regions)}."""
+    out = {}
+    for k, name in enumerate(STAGES):
+        ms, cnt = C.c_double(0.0), C.c_int64(0)
+        check(lib.mb200_profile_read(k, C.byref(ms), C.byref(cnt)), "profile_read")
+        out[name] = (ms.value, cnt.value)
+    return out

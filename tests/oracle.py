@@ -244,6 +244,36 @@ def abc_flow_force(pos):
     return F
 
 
+# ---- whole step (composition of the pieces above; the loop body of
+# scrap/parameter_interface/NGPSpheresLCP.cpp:1135-1292) ---------------------------------------------------------
+def collision_step(state, w, links, buffer, filt, mu, dt, tol, max_it, fixed, F_ext):
+    """One collision step composed from the oracle pieces; `links` carries (pairs, ref_center) between steps."""
+    c, q = state
+    kind, L, r = w.get("kind"), w.get("length"), w["radius"]
+    if links is not None and not filt and moved_too_much(c, links[1], buffer):
+        links = None  # rebuild trigger of GenNeighborLinks::generate (GenNeighborLinkers.hpp:603-615)
+    rebuilt = links is None
+    if links is None:
+        S = search_radii(r, buffer, kind, L)
+        pairs = search(c, S)
+        if filt and kind is not None:
+            pairs = filter_shape_distance(pairs, c, q, r, L, kind, 2 * buffer)
+        links = (pairs, c.copy())
+    pairs = links[0]
+    arms = kind is not None
+    phi, nrm, ai, aj = narrow_phase(pairs, c, r, q, L, kind, arms)
+    Uext = Wext = None
+    if F_ext is not None:
+        Uext, Wext = apply_M(r, mu, F_ext, np.zeros_like(F_ext) if arms else None, q, kind)
+    out = resolve_collisions(len(r), pairs, nrm, r, mu, dt, tol, max_it, phi, fixed_iters=fixed, arm_i=ai,
+                                    arm_j=aj, quat=q, kind=kind, U_ext=Uext, W_ext=Wext)
+    U = out["U"] + (Uext if Uext is not None else 0.0)
+    Wt = (out["W"] + (Wext if Wext is not None else 0.0)) if arms else None
+    c2, q2 = euler_update(c, U, dt, q, kind, Wt)
+    out["rebuilt"] = rebuilt
+    return (c2, q2), links, out, U
+
+
 # ---- math::convex (both libraries) ------------------------------------------------------------------------------------
 def solve_cqpp_dense(A, q, x0, space_kind=1, lo=0.0, hi=0.0, max_iters=1000, tol=1e-8, resid_kind=0, lib=None,
                      prefix="orc_"):

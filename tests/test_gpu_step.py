@@ -86,33 +86,18 @@ def test_euler_update(cuda):
     assert np.array_equal(host(q)[:10], w["quat"][:10])
 
 
+def test_abc_flow_force(cuda):
+    from mundy_b200 import ops
+    w = wl.polydisperse_spheres(5000)
+    F0 = np.random.default_rng(0).normal(size=(5000, 3))
+    F = ops.abc_flow_force(dev(w["center"]), dev(F0))
+    Fo = F0.copy()
+    Fo += oracle.abc_flow_force(w["center"])
+    assert np.max(np.abs(host(F) - Fo)) <= 1e-14  # sin/cos: CUDA libdevice vs glibc, <= 2 ulp on O(1) values
+
+
 # ---- whole step -----------------------------------------------------------------------------------------------------
-def oracle_step(state, w, links, buffer, filt, mu, dt, tol, max_it, fixed, F_ext):
-    """One collision step composed from the oracle pieces; `links` carries (pairs, ref_center) between steps."""
-    c, q = state
-    kind, L, r = w.get("kind"), w.get("length"), w["radius"]
-    if links is not None and not filt and oracle.moved_too_much(c, links[1], buffer):
-        links = None  # rebuild trigger of GenNeighborLinks::generate (GenNeighborLinkers.hpp:603-615)
-    rebuilt = links is None
-    if links is None:
-        S = oracle.search_radii(r, buffer, kind, L)
-        pairs = oracle.search(c, S)
-        if filt and kind is not None:
-            pairs = oracle.filter_shape_distance(pairs, c, q, r, L, kind, 2 * buffer)
-        links = (pairs, c.copy())
-    pairs = links[0]
-    arms = kind is not None
-    phi, nrm, ai, aj = oracle.narrow_phase(pairs, c, r, q, L, kind, arms)
-    Uext = Wext = None
-    if F_ext is not None:
-        Uext, Wext = oracle.apply_M(r, mu, F_ext, np.zeros_like(F_ext) if arms else None, q, kind)
-    out = oracle.resolve_collisions(len(r), pairs, nrm, r, mu, dt, tol, max_it, phi, fixed_iters=fixed, arm_i=ai,
-                                    arm_j=aj, quat=q, kind=kind, U_ext=Uext, W_ext=Wext)
-    U = out["U"] + (Uext if Uext is not None else 0.0)
-    Wt = (out["W"] + (Wext if Wext is not None else 0.0)) if arms else None
-    c2, q2 = oracle.euler_update(c, U, dt, q, kind, Wt)
-    out["rebuilt"] = rebuilt
-    return (c2, q2), links, out, U
+oracle_step = oracle.collision_step
 
 
 STEP_CASES = [("spheres", wl.polydisperse_spheres, dict(n=8000, phi=0.25), 0.5, False),
