@@ -137,7 +137,7 @@ class NeighborLinks:
         check(lib.mb200_neighbor_links_create(C.byref(self._h)), "neighbor_links_create")
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # lib is None during interpreter shutdown
             lib.mb200_neighbor_links_destroy(self._h)
             self._h = None
 

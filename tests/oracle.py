@@ -170,6 +170,11 @@ def moved_too_much(pos, pos_at_build, buffer):
     return bool(_call(orc, "orc_moved_too_much", len(pos), _a(pos), _a(pos_at_build), float(buffer), restype=C.c_int))
 
 
+def moved_too_much_shapes(pos, quat, length, kind, pos_at_build, quat_at_build, buffer):
+    return bool(_call(orc, "orc_moved_too_much_shapes", len(pos), _a(pos), _a(quat), _a(length), _a(kind, _i),
+                      _a(pos_at_build), _a(quat_at_build), float(buffer), restype=C.c_int))
+
+
 def narrow_phase(pairs, pos, r, quat=None, length=None, kind=None, arms=False):
     pairs = _a(pairs, _i)
     m = len(pairs)
@@ -250,15 +255,19 @@ def collision_step(state, w, links, buffer, filt, mu, dt, tol, max_it, fixed, F_
     """One collision step composed from the oracle pieces; `links` carries (pairs, ref_center) between steps."""
     c, q = state
     kind, L, r = w.get("kind"), w.get("length"), w["radius"]
-    if links is not None and not filt and moved_too_much(c, links[1], buffer):
-        links = None  # rebuild trigger of GenNeighborLinks::generate (GenNeighborLinkers.hpp:603-615)
+    if links is not None:  # rebuild trigger of GenNeighborLinks::generate (GenNeighborLinkers.hpp:603-615)
+        if filt and kind is not None:
+            if moved_too_much_shapes(c, q, L, kind, links[1], links[2], buffer):
+                links = None
+        elif moved_too_much(c, links[1], buffer):
+            links = None
     rebuilt = links is None
     if links is None:
         S = search_radii(r, buffer, kind, L)
         pairs = search(c, S)
         if filt and kind is not None:
             pairs = filter_shape_distance(pairs, c, q, r, L, kind, 2 * buffer)
-        links = (pairs, c.copy())
+        links = (pairs, c.copy(), None if q is None else q.copy())
     pairs = links[0]
     arms = kind is not None
     phi, nrm, ai, aj = narrow_phase(pairs, c, r, q, L, kind, arms)

@@ -195,11 +195,21 @@ def test_bbpgd_converged(cuda, name, maker, kw, buffer, p):
     phi_d, gam_d = dev(phi), torch.zeros(len(pairs), dtype=torch.float64, device="cuda")
     res, F, T, U, W = ops.resolve_collisions(op, phi_d, gam_d, p["tol"], 10000)
     assert res.converged and res.max_abs_projected_sep < p["tol"] and want["res"] < p["tol"]
-    assert res.ite_count == want["it"], (res.ite_count, want["it"])
-    # post-solve relative agreement; 1e-8 leaves room for the rounding-order amplification over ~100 BB iterations
-    assert rel(host(gam_d), want["gamma"]) <= 1e-8
-    assert rel(host(F), want["F"]) <= 1e-8 and rel(host(U), want["U"]) <= 1e-8
-    print(name, "iters", res.ite_count, "rel gamma", rel(host(gam_d), want["gamma"]), "rel U", rel(host(U), want["U"]))
+    # BBPGD is non-monotone: over ~1000 iterations the rounding order of the three global sums (tree reduction here,
+    # thread-chunked in the oracle, unspecified in Kokkos) can move the iteration at which res < tol first holds.
+    # (observed: 1283 here vs 1281 / 1269 for the oracle summing serially / over 16 OpenMP threads)
+    assert abs(res.ite_count - want["it"]) <= max(0, want["it"] // 20), (res.ite_count, want["it"])
+    if res.ite_count == want["it"]:
+        # post-solve relative agreement; 1e-8 leaves room for the rounding-order amplification over the BB iterations
+        assert rel(host(gam_d), want["gamma"]) <= 1e-8
+        assert rel(host(F), want["F"]) <= 1e-8 and rel(host(U), want["U"]) <= 1e-8
+    # in every case the GPU's gamma must satisfy the reference's own stopping test when the ORACLE evaluates it
+    chk = oracle.resolve_collisions(n, pairs, nrm, w["radius"], p["mu"], p["dt"], p["tol"], 10000, phi,
+                                    gamma0=host(gam_d), fixed_iters=0, arm_i=ai, arm_j=aj, quat=w.get("quat"),
+                                    kind=w.get("kind"))
+    assert chk["res"] < p["tol"] and abs(chk["res"] - res.max_abs_projected_sep) <= 1e-9 * p["tol"]
+    assert rel(host(U), chk["U"]) <= RTOL and rel(host(F), chk["F"]) <= RTOL
+    print(name, "iters", res.ite_count, want["it"], "rel gamma", rel(host(gam_d), want["gamma"]))
 
 
 def test_bbpgd_external_velocity_and_warm_start(cuda):
