@@ -291,13 +291,13 @@ def run_b200(args):
     stage_out = {}
     if stages:
         # algorithmic bytes per launch (DESIGN.md "Kernels"): C contacts, n bodies, 6-DOF
-        alg = {"lcp_rate": 120.0 * C + 64.0 * n, "lcp_body": 96.0 * C + 104.0 * n, "lcp_gamma": 32.0 * C}
+        alg = {"lcp_rate": 128.0 * C + 64.0 * n, "lcp_body": 120.0 * C + 104.0 * n}
         for name, (tot_ms, cnt) in stages.items():
             stage_out[name] = {"ms_total": round(tot_ms, 4), "regions": cnt}
             if name in alg and cnt > 0:
                 gbs = alg[name] / (tot_ms / cnt * 1e-3) / 1e9
                 stage_out[name].update({"alg_bytes": alg[name], "gbs": round(gbs, 1), "frac": round(gbs / peak, 4)})
-        dom = max(("lcp_rate", "lcp_body", "lcp_gamma"), key=lambda k: stages[k][0])
+        dom = max(("lcp_rate", "lcp_body"), key=lambda k: stages[k][0])
         tot_ms, cnt = stages[dom]
         if cnt > 0:
             achieved = alg[dom] / (tot_ms / cnt * 1e-3) / 1e9
@@ -305,8 +305,8 @@ def run_b200(args):
                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                         "launches": cnt, "avg_us": 1e3 * tot_ms / cnt,
                         "share_of_step": tot_ms / ms}
-            it_ms = sum(stages[k][0] for k in ("lcp_rate", "lcp_body", "lcp_gamma"))
-            its = stages["lcp_gamma"][1]
+            it_ms = sum(stages[k][0] for k in ("lcp_rate", "lcp_body"))
+            its = stages["lcp_rate"][1]  # operator applications (one body pass + one contact pass each)
             if its > 0:
                 it_bytes = 120.0 * C + 240.0 * n  # fused-ideal bytes of one rod BBPGD iteration
                 roofline["lcp_iteration"] = {"alg_bytes": it_bytes, "avg_us": 1e3 * it_ms / its,

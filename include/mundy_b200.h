@@ -299,9 +299,9 @@ enum mb200_stage {
   MB200_STAGE_BROADPHASE = 1, /* link rebuild: keys, sort, cell table, pair search, incidence lists      */
   MB200_STAGE_PACK = 2,       /* bodies -> Morton-order records and solver inputs   one region per step   */
   MB200_STAGE_NARROW = 3,     /* narrow phase                                        one region per step   */
-  MB200_STAGE_LCP_GAMMA = 4,  /* BBPGD: gamma update                                 one region per launch */
-  MB200_STAGE_LCP_BODY = 5,   /* BBPGD: F = D gamma, U = M F                         one region per launch */
-  MB200_STAGE_LCP_RATE = 6,   /* BBPGD: g = D^T U, residual, BB dots                 one region per launch */
+  MB200_STAGE_LCP_SETUP = 4,  /* BBPGD: mobility records, initial state, phi0 += dt D^T U_ext   per solve */
+  MB200_STAGE_LCP_BODY = 5,   /* BBPGD: gamma update, F = D gamma, U = M F           one region per launch */
+  MB200_STAGE_LCP_RATE = 6,   /* BBPGD: gamma update, g = D^T U, residual, BB dots   one region per launch */
   MB200_STAGE_EULER = 7,      /* velocity totals, Euler update, scatter to the caller's order            */
   MB200_STAGE_COUNT = 8
 };

@@ -186,7 +186,7 @@ struct __align__(32) D4 {
 };
 __device__ inline D4 ldg256(const D4* p) {  // read-only path
   D4 r;
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+  asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
   return r;
 }
 __device__ inline D4 ld256(const D4* p) {

@@ -19,7 +19,26 @@ struct Incidence {
 };
 int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, Incidence* inc);
 
-// The BBPGD solve on an already-built incidence structure (used by mb200_resolve_collisions and the step).
+// The BBPGD solve on contact records (layout: lcp_solve.cu header). rec is modified when U_ext != NULL (phi0 correction).
+// F,T,U,W are written in the order of the bodies the records index; U/W hold the collision velocity only.
+struct RecordSystem {
+  int64_t n, npairs;
+  bool six;
+  const int2* pairs;  // [npairs]
+  D4* rec;            // [npairs] (3-DOF) or [3 npairs] (6-DOF)
+  const double* quat;
+  const double* radius;
+  const int32_t* kind;
+  double mu, dt;
+};
+int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& inc, const mb200_lcp_params* params,
+                    const double* U_ext, const double* W_ext, const double* gamma0, double* gamma_out,
+                    double* phi0_out, double* F, double* T, double* U, double* W, mb200_collision_result* result_h);
+// Narrow phase straight into contact records (the step's path).
+int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const D4* b0, const D4* b1, bool six,
+                            D4* rec);
+
+// The BBPGD solve on caller-layout arrays and an already-built incidence structure (used by mb200_resolve_collisions and the step).
 int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const Incidence& inc,
                             const mb200_lcp_params* params, const double* U_ext, const double* W_ext, double* phi0,
                             double* gamma, double* F, double* T, double* U, double* W,

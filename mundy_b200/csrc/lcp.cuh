@@ -60,12 +60,11 @@ __device__ inline void body_wrench(int64_t b, const int64_t* __restrict__ ptr, c
   T = V3{t0, t1, t2};
 }
 
-// U = M F, W = M_r T for one body. `rod` selects the anisotropic form (axis = q (x) z_hat).
-__device__ inline void body_mobility(const Mob& m, bool rod, const Q4& q, const V3& F, const V3& T, V3& U, V3& W) {
+// U = M F, W = M_r T for one body whose axis a = q (x) z_hat is known. `rod` selects the anisotropic form.
+__device__ inline void body_mobility_axis(const Mob& m, bool rod, const V3& a, const V3& F, const V3& T, V3& U, V3& W) {
   if (!rod) {
     U = V3{m.inv_para * F.x, m.inv_para * F.y, m.inv_para * F.z};
   } else {
-    const V3 a = qrot(q, V3{0.0, 0.0, 1.0});
     const double av[3] = {a.x, a.y, a.z};
     double u[3];
 #pragma unroll
@@ -82,6 +81,10 @@ __device__ inline void body_mobility(const Mob& m, bool rod, const Q4& q, const 
     U = V3{u[0], u[1], u[2]};
   }
   W = V3{m.inv_rot * T.x, m.inv_rot * T.y, m.inv_rot * T.z};
+}
+__device__ inline void body_mobility(const Mob& m, bool rod, const Q4& q, const V3& F, const V3& T, V3& U, V3& W) {
+  const V3 a = rod ? qrot(q, V3{0.0, 0.0, 1.0}) : V3{0.0, 0.0, 1.0};
+  body_mobility_axis(m, rod, a, F, T, U, W);
 }
 
 // gdot of one contact.

@@ -1,16 +1,27 @@
 // E1. Driver BBPGD (scrap/lcp_spheres/KokkosLCP.cpp:675-876), device-resident.
 //
-// One iteration = three kernels, no host round trip (the reference blocks the host twice per iteration):
-//   gamma_update : gamma = max(gamma_prev - alpha (phi0 + dt g), 0)                 contact pass, 32 B/contact
-//   body_pass    : F = D gamma (ordered per-body sums over the incidence list, no atomics), U = M F
-//                  -> 32-byte velocity records                                        body pass
-//   rate_pass    : g = D^T U, residual max, the three BB dot products; the last CTA to finish reduces the per-CTA
-//                  partials in a fixed order and advances the scalar state (alpha, residual, done)   contact pass
-// Every kernel returns immediately once `done` is set, so the host enqueues iterations in batches and only reads
-// the 48-byte state back between batches.
+// Data layout in HBM (all internal; Morton order when called from the step):
+//   contact records, 32 bytes each (one DRAM sector, moved with one 256-bit load):
+//       R0 = {nx, ny, nz, phi0}                       3-DOF and 6-DOF
+//       R1 = {arm_i.x, arm_i.y, arm_i.z, (i, j)}      6-DOF only; the int32 pair rides in the 4th slot
+//       R2 = {arm_j.x, arm_j.y, arm_j.z, 0}           6-DOF only
+//     stored interleaved: rec[3 c + k] (6-DOF) or rec[c] (3-DOF; the pair comes from the int2 list)
+//   contact state {gamma, g} as double2, ping-pong between two buffers (no roll-forward copies, K13)
+//   body mobility record {axis.x, axis.y, axis.z, +r (rod) | -r (sphere)}, axis = q (x) z_hat, built once per solve
+//   body velocity records {U, 0} (+ {W, 0} for 6-DOF): 64 MB at 10^6 rods, gathered by the contact pass out of L2
+//
+// One iteration = two kernels, no host round trip (the reference blocks the host twice per iteration):
+//   body_pass : for every body, gamma of its incident contacts is re-derived from the previous state
+//               (gamma = max(gamma_prev - alpha (phi0 + dt g_prev), 0), KokkosLCP.cpp:655-664), the contact wrenches
+//               are formed by all threads of the CTA in parallel (independent gathers), staged in shared memory and
+//               then summed per body in ascending (contact, side) order: F = D gamma without atomics, bit-identical to
+//               a serial loop; U = M F; velocity records written.
+//   rate_pass : per contact: the same gamma, g = D^T U, new state, residual max and the three BB dot products;
+//               the last CTA to finish reduces the per-CTA partials in index order and advances alpha / done.
+// Every kernel returns at once when `done` is set, so the host enqueues iterations in batches and reads the 48-byte
+// solver state back between batches only.
 #include "internal.cuh"
 #include "lcp.cuh"
-#include "tile_io.cuh"
 
 namespace mb200 {
 namespace {
@@ -27,17 +38,12 @@ struct LcpState {
 
 struct LcpArgs {  // everything the iteration kernels need; passed by value
   int64_t n, npairs;
-  const int2* pairs;
-  const double* normal;
-  const double* arm_i;
-  const double* arm_j;
-  const double* quat;
-  const double* radius;
-  const int32_t* kind;
+  const int2* pairs;  // 3-DOF only
+  const D4* rec;      // contact records
+  const D4* mob;      // [n] mobility records
   const int64_t* inc_ptr;
   const uint32_t* inc_list;
-  const double* phi0;
-  D4* vel;  // [n] (3-DOF) or [2n] (6-DOF: U record then W record per body)
+  D4* vel;  // [n] (3-DOF) or [2n] (6-DOF)
   double mu, dt, tol;
   int32_t fixed;   // ignore tol
   int32_t it_cap;  // max iterations (or the fixed count)
@@ -45,40 +51,201 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
   double* partials;  // [4 * rate grid]
 };
 
-constexpr int kRateThreads = kTile;
+__device__ inline double2 ldg128(const double2* p) {
+  double2 r;
+  asm("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+  return r;
+}
 
+__device__ inline int2 pair_of(const D4& r1) {
+  const long long b = __double_as_longlong(r1.w);
+  return make_int2(static_cast<int>(b & 0xffffffffll), static_cast<int>(b >> 32));
+}
+__device__ inline double pair_bits(int i, int j) {
+  return __longlong_as_double((static_cast<long long>(j) << 32) | static_cast<long long>(static_cast<uint32_t>(i)));
+}
+
+// gamma of one contact for the current iteration (KokkosLCP.cpp:655-664). MODE 0: the state already holds it.
+template <int MODE>
+__device__ inline double gamma_of(const double2& sp, double phi0, double alpha, double dt, int first) {
+  if (MODE == 0) return sp.x;
+  const double gc = first ? 0.0 : sp.y;  // :756 passes signed_sep_dot (zeros) on the first iteration
+  const double sep_new = phi0 + dt * gc;
+  return fmax(sp.x - alpha * sep_new, 0.0);
+}
+
+// ---- prologue / epilogue kernels ---------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-    gamma_update_kernel(int64_t npairs, const double* __restrict__ gamma_prev, const double* __restrict__ phi0,
-                        const double* __restrict__ g, int first, double dt, const LcpState* __restrict__ state,
-                        double* __restrict__ gamma) {
-  if (state->done) return;
-  const double alpha = state->alpha;
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  for (int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; c < npairs; c += stride) {
-    const double gc = first ? 0.0 : g[c];  // KokkosLCP.cpp:756 uses signed_sep_dot (zeros) on the first iteration
-    const double sep_new = phi0[c] + dt * gc;
-    gamma[c] = fmax(gamma_prev[c] - alpha * sep_new, 0.0);
+    mobility_records_kernel(int64_t n, const double* __restrict__ radius, const double* __restrict__ quat,
+                            const int32_t* __restrict__ kind, D4* __restrict__ mob) {
+  const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (b >= n) return;
+  const double r = radius[b];
+  const bool rod = quat && kind && kind[b] == MB200_SPHEROCYLINDER;
+  V3 a{0.0, 0.0, 1.0};
+  if (rod) a = qrot(ldq(quat, b), V3{0.0, 0.0, 1.0});
+  st256(mob + b, D4{a.x, a.y, a.z, rod ? r : -r});
+}
+
+// caller layout -> records and initial state {gamma0, 0}
+template <bool SIX>
+__global__ void __launch_bounds__(256)
+    pack_contacts_kernel(int64_t npairs, const int2* __restrict__ pairs, const double* __restrict__ normal,
+                         const double* __restrict__ arm_i, const double* __restrict__ arm_j,
+                         const double* __restrict__ phi0, D4* __restrict__ rec) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c >= npairs) return;
+  const V3 n = ld3(normal, c);
+  if (SIX) {
+    const int2 p = pairs[c];
+    const V3 ai = ld3(arm_i, c), aj = ld3(arm_j, c);
+    st256(rec + 3 * c, D4{n.x, n.y, n.z, phi0[c]});
+    st256(rec + 3 * c + 1, D4{ai.x, ai.y, ai.z, pair_bits(p.x, p.y)});
+    st256(rec + 3 * c + 2, D4{aj.x, aj.y, aj.z, 0.0});
+  } else {
+    st256(rec + c, D4{n.x, n.y, n.z, phi0[c]});
   }
 }
 
-// FINAL: also writes F,T,U,W in the caller's layout and reduces max |U| into state->vmax (single launch at the end).
-template <bool SIX, bool FINAL>
-__global__ void __launch_bounds__(128)
-    body_pass_kernel(LcpArgs a, const double* __restrict__ gamma, double* __restrict__ F, double* __restrict__ T,
-                     double* __restrict__ U, double* __restrict__ W, const double* __restrict__ U_ext,
-                     const double* __restrict__ W_ext) {
+template <bool SIX>
+__global__ void __launch_bounds__(256)
+    unpack_contacts_kernel(int64_t npairs, const D4* __restrict__ rec, const double2* __restrict__ state,
+                           double* __restrict__ phi0, double* __restrict__ gamma) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c >= npairs) return;
+  if (phi0) phi0[c] = ldg256(rec + (SIX ? 3 * c : c)).w;
+  if (gamma) gamma[c] = state[c].x;
+}
+
+__global__ void __launch_bounds__(256) init_state_kernel(int64_t npairs, const double* __restrict__ gamma0,
+                                                         double2* __restrict__ state) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c < npairs) state[c] = make_double2(gamma0 ? gamma0[c] : 0.0, 0.0);
+}
+
+// phi0 += dt * D^T (U_ext, W_ext)   scrap/parameter_interface/NGPSpheresLCP.cpp:751-756
+template <bool SIX>
+__global__ void __launch_bounds__(256)
+    ext_correction_kernel(int64_t npairs, const int2* __restrict__ pairs, D4* rec, const double* __restrict__ U_ext,
+                          const double* __restrict__ W_ext, double dt) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c >= npairs) return;
+  D4* r0p = rec + (SIX ? 3 * c : c);
+  D4 r0 = ld256(r0p);
+  const V3 n{r0.x, r0.y, r0.z};
+  V3 wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
+  int2 p;
+  const bool six = SIX && W_ext;
+  if (SIX) {
+    const D4 r1 = ld256(rec + 3 * c + 1), r2 = ld256(rec + 3 * c + 2);
+    p = pair_of(r1);
+    ai = V3{r1.x, r1.y, r1.z}, aj = V3{r2.x, r2.y, r2.z};
+    if (six) wi = ld3(W_ext, p.x), wj = ld3(W_ext, p.y);
+  } else {
+    p = pairs[c];
+  }
+  const double g = six ? contact_rate<true>(n, ld3(U_ext, p.x), ld3(U_ext, p.y), wi, wj, ai, aj)
+                       : contact_rate<false>(n, ld3(U_ext, p.x), ld3(U_ext, p.y), wi, wj, ai, aj);
+  r0.w += dt * g;
+  st256(r0p, r0);
+}
+
+// ---- iteration kernels ---------------------------------------------------------------------------------------------
+constexpr int kBodyThreads = 128;
+constexpr int kBodiesPerCta = 64;
+constexpr int kCap = 512;  // incidence entries staged per round (avg ~6.4 per rod at cfg3 => one round per CTA)
+constexpr int kUnroll = 4;  // entries in flight per thread
+
+// MODE 0: gamma is read from the state (initial pass and final pass). MODE 1: gamma re-derived from the previous state.
+// FINAL: also writes F,T,U,W in the solver's body order and reduces max |U| into state->vmax (single launch at the end).
+template <bool SIX, int MODE, bool FINAL>
+__global__ void __launch_bounds__(kBodyThreads)
+    body_pass_kernel(LcpArgs a, int first, const double2* __restrict__ st_prev, double* __restrict__ F,
+                     double* __restrict__ T, double* __restrict__ U, double* __restrict__ W,
+                     const double* __restrict__ U_ext, const double* __restrict__ W_ext) {
   if (!FINAL && a.state->done) return;
+  constexpr int NC = SIX ? 6 : 3;
+  __shared__ double s_w[NC][kCap];
   __shared__ double sh[33];
-  const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const double alpha = (MODE == 1) ? a.state->alpha : 0.0;
+  const int t = threadIdx.x;
+  const int64_t b0 = static_cast<int64_t>(blockIdx.x) * kBodiesPerCta;
+  const int nb = static_cast<int>(min(static_cast<int64_t>(kBodiesPerCta), a.n - b0));
+  __shared__ int64_t s_ptr[kBodiesPerCta + 1];
+  if (t <= nb) s_ptr[t] = a.inc_ptr[b0 + t];
+  D4 mr{0.0, 0.0, 1.0, -1.0};
+  if (t < nb) mr = ldg256(a.mob + b0 + t);  // needed only at the end: issued now to overlap with everything else
+  __syncthreads();
+  const int64_t e_begin = s_ptr[0], e_end = s_ptr[nb];
+  int64_t my_beg = 0, my_end = 0;
+  if (t < nb) my_beg = s_ptr[t], my_end = s_ptr[t + 1];
+  double acc[NC];
+#pragma unroll
+  for (int k = 0; k < NC; ++k) acc[k] = 0.0;
+
+  for (int64_t rb = e_begin; rb < e_end; rb += kCap) {
+    const int cnt = static_cast<int>(min(static_cast<int64_t>(kCap), e_end - rb));
+    // phase 1: every thread forms the wrench of up to kUnroll (contact, side) entries; the loads of all of them are
+    // issued before the first use (independent gathers: memory-level parallelism instead of occupancy)
+    for (int k0 = 0; k0 < cnt; k0 += kBodyThreads * kUnroll) {
+      uint32_t e[kUnroll];
+      double2 sp[kUnroll];
+      D4 r0[kUnroll], ra[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int k = k0 + u * kBodyThreads + t;
+        e[u] = (k < cnt) ? __ldg(a.inc_list + rb + k) : 0xffffffffu;
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (e[u] != 0xffffffffu) {
+          const int64_t c = e[u] >> 1;
+          sp[u] = ldg128(st_prev + c);
+          r0[u] = ldg256(a.rec + (SIX ? 3 * c : c));
+          if (SIX) ra[u] = ldg256(a.rec + 3 * c + 1 + (e[u] & 1u));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (e[u] != 0xffffffffu) {
+          const int k = k0 + u * kBodyThreads + t;
+          const int is_j = e[u] & 1u;
+          const double g = gamma_of<MODE>(sp[u], r0[u].w, alpha, a.dt, first);
+          // n_I = n, n_J = -n: F += -gamma n_side, T += -gamma (r_side x n_side)   (scrap/UnitTestMundy.cpp:652-674)
+          const double mx = is_j ? -r0[u].x : r0[u].x, my = is_j ? -r0[u].y : r0[u].y, mz = is_j ? -r0[u].z : r0[u].z;
+          s_w[0][k] = -g * mx;
+          s_w[1][k] = -g * my;
+          s_w[2][k] = -g * mz;
+          if (SIX) {
+            s_w[3][k] = -g * (ra[u].y * mz - ra[u].z * my);
+            s_w[4][k] = -g * (ra[u].z * mx - ra[u].x * mz);
+            s_w[5][k] = -g * (ra[u].x * my - ra[u].y * mx);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // phase 2: one thread per body adds its entries in ascending (contact, side) order
+    if (t < nb) {
+      const int lo = static_cast<int>(max(my_beg, rb) - rb);
+      const int hi = static_cast<int>(min(my_end, rb + cnt) - rb);
+      for (int k = lo; k < hi; ++k) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) acc[j] += s_w[j][k];
+      }
+    }
+    __syncthreads();
+  }
+
   double speed = 0.0;
-  if (b < a.n) {
-    V3 f, t;
-    body_wrench<SIX>(b, a.inc_ptr, a.inc_list, gamma, a.normal, a.arm_i, a.arm_j, f, t);
-    const Mob m = mobility_of(a.radius[b], a.mu);
-    const bool rod = SIX && a.quat && a.kind && a.kind[b] == MB200_SPHEROCYLINDER;
-    const Q4 q = rod ? ldq(a.quat, b) : Q4{1.0, 0.0, 0.0, 0.0};
+  if (t < nb) {
+    const int64_t b = b0 + t;
+    const bool rod = SIX && mr.w > 0.0;
+    const Mob m = mobility_of(fabs(mr.w), a.mu);
+    const V3 f{acc[0], acc[1], acc[2]};
+    const V3 tq = SIX ? V3{acc[3], acc[4], acc[5]} : V3{0.0, 0.0, 0.0};
     V3 u, w;
-    body_mobility(m, rod, q, f, t, u, w);
+    body_mobility_axis(m, rod, V3{mr.x, mr.y, mr.z}, f, tq, u, w);
     if (!FINAL) {
       if (SIX) {
         st256(a.vel + 2 * b, D4{u.x, u.y, u.z, 0.0});
@@ -89,7 +256,7 @@ __global__ void __launch_bounds__(128)
     } else {
       speed = sqrt(u.x * u.x + u.y * u.y + u.z * u.z);  // KokkosLCP.cpp:861-872 (collision velocity only)
       if (F) st3(F, b, f);
-      if (SIX && T) st3(T, b, t);
+      if (SIX && T) st3(T, b, tq);
       if (U_ext) u = u + ld3(U_ext, b);  // U += U_col on top of the external velocity (NGPSpheresLCP.cpp:867-877)
       if (SIX && W_ext) w = w + ld3(W_ext, b);
       if (U) st3(U, b, u);
@@ -98,67 +265,57 @@ __global__ void __launch_bounds__(128)
   }
   if (FINAL) {
     const double m = block_max(speed, sh, 0.0);
-    if (threadIdx.x == 0) {
-      // non-negative doubles order like their bit patterns
-      atomicMax(reinterpret_cast<unsigned long long*>(&a.state->vmax), static_cast<unsigned long long>(__double_as_longlong(m)));
+    if (threadIdx.x == 0) {  // non-negative doubles order like their bit patterns
+      atomicMax(reinterpret_cast<unsigned long long*>(&a.state->vmax),
+                static_cast<unsigned long long>(__double_as_longlong(m)));
     }
   }
 }
 
-// MODE 0: initial pass (g_out = D^T M D gamma_0, residual only). MODE 1: iteration pass (residual + BB dots).
+constexpr int kRateThreads = 256;
+
+// MODE 0: initial pass (state holds gamma_0; g_0 = D^T M D gamma_0, residual only). MODE 1: iteration pass.
 template <bool SIX, int MODE>
 __global__ void __launch_bounds__(kRateThreads)
-    rate_pass_kernel(LcpArgs a, int it, const double* __restrict__ gamma, const double* __restrict__ gamma_prev,
-                     const double* __restrict__ g_prev, double* __restrict__ g_out) {
+    rate_pass_kernel(LcpArgs a, int it, int first, const double2* __restrict__ st_prev, double2* __restrict__ st_cur) {
   if (a.state->done) return;
-  __shared__ __align__(16) double s_n[3 * kTile];
-  __shared__ __align__(16) double s_ai[SIX ? 3 * kTile : 2];
-  __shared__ __align__(16) double s_aj[SIX ? 3 * kTile : 2];
   __shared__ double sh[33];
   __shared__ bool is_last;
+  const double alpha = (MODE == 1) ? a.state->alpha : 0.0;
   double res = -1.0, xx = 0.0, xg = 0.0, gg = 0.0;
-  const int64_t ntiles = (a.npairs + kTile - 1) / kTile;
   const int t = threadIdx.x;
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t base = tile * kTile;
-    const int cnt = static_cast<int>(min(static_cast<int64_t>(kTile), a.npairs - base));
-    load_tile<3>(s_n, a.normal, base, cnt);
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kRateThreads;
+  for (int64_t c = static_cast<int64_t>(blockIdx.x) * kRateThreads + t; c < a.npairs; c += stride) {
+    const double2 sp = ldg128(st_prev + c);
+    const D4 r0 = ldg256(a.rec + (SIX ? 3 * c : c));
+    const V3 n{r0.x, r0.y, r0.z};
+    V3 ui, uj, wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
     if (SIX) {
-      load_tile<3>(s_ai, a.arm_i, base, cnt);
-      load_tile<3>(s_aj, a.arm_j, base, cnt);
-    }
-    __syncthreads();
-    if (t < cnt) {
-      const int64_t c = base + t;
+      const D4 r1 = ldg256(a.rec + 3 * c + 1), r2 = ldg256(a.rec + 3 * c + 2);
+      const int2 p = pair_of(r1);
+      const D4 v0 = ldg256(a.vel + 2 * p.x), v1 = ldg256(a.vel + 2 * p.x + 1);
+      const D4 v2 = ldg256(a.vel + 2 * p.y), v3 = ldg256(a.vel + 2 * p.y + 1);
+      ui = V3{v0.x, v0.y, v0.z}, wi = V3{v1.x, v1.y, v1.z};
+      uj = V3{v2.x, v2.y, v2.z}, wj = V3{v3.x, v3.y, v3.z};
+      ai = V3{r1.x, r1.y, r1.z}, aj = V3{r2.x, r2.y, r2.z};
+    } else {
       const int2 p = __ldg(a.pairs + c);
-      const V3 n{s_n[3 * t], s_n[3 * t + 1], s_n[3 * t + 2]};
-      V3 ui, uj, wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
-      if (SIX) {
-        const D4 r0 = ld256(a.vel + 2 * p.x), r1 = ld256(a.vel + 2 * p.x + 1);
-        const D4 r2 = ld256(a.vel + 2 * p.y), r3 = ld256(a.vel + 2 * p.y + 1);
-        ui = V3{r0.x, r0.y, r0.z}, wi = V3{r1.x, r1.y, r1.z};
-        uj = V3{r2.x, r2.y, r2.z}, wj = V3{r3.x, r3.y, r3.z};
-        ai = V3{s_ai[3 * t], s_ai[3 * t + 1], s_ai[3 * t + 2]};
-        aj = V3{s_aj[3 * t], s_aj[3 * t + 1], s_aj[3 * t + 2]};
-      } else {
-        const D4 r0 = ld256(a.vel + p.x), r2 = ld256(a.vel + p.y);
-        ui = V3{r0.x, r0.y, r0.z}, uj = V3{r2.x, r2.y, r2.z};
-      }
-      const double g = contact_rate<SIX>(n, ui, uj, wi, wj, ai, aj);
-      g_out[c] = g;
-      const double gam = gamma[c];
-      const double sep_new = a.phi0[c] + a.dt * g;  // KokkosLCP.cpp:500-521
-      const double v = (gam < 1e-12) ? fabs(fmin(sep_new, 0.0)) : fabs(sep_new);
-      res = fmax(res, v);
-      if (MODE == 1) {  // KokkosLCP.cpp:536-556
-        const double xd = gam - gamma_prev[c];
-        const double gd = a.dt * (g - g_prev[c]);
-        xx += xd * xd;
-        xg += xd * gd;
-        gg += gd * gd;
-      }
+      const D4 v0 = ldg256(a.vel + p.x), v2 = ldg256(a.vel + p.y);
+      ui = V3{v0.x, v0.y, v0.z}, uj = V3{v2.x, v2.y, v2.z};
     }
-    __syncthreads();
+    const double gam = gamma_of<MODE>(sp, r0.w, alpha, a.dt, first);
+    const double g = contact_rate<SIX>(n, ui, uj, wi, wj, ai, aj);
+    st_cur[c] = make_double2(gam, g);
+    const double sep_new = r0.w + a.dt * g;  // KokkosLCP.cpp:500-521
+    const double v = (gam < 1e-12) ? fabs(fmin(sep_new, 0.0)) : fabs(sep_new);
+    res = fmax(res, v);
+    if (MODE == 1) {  // KokkosLCP.cpp:536-556
+      const double xd = gam - sp.x;
+      const double gd = a.dt * (g - sp.y);
+      xx += xd * xd;
+      xg += xd * gd;
+      gg += gd * gd;
+    }
   }
   // per-CTA partials, then the last CTA reduces them in index order (deterministic)
   res = block_max(res, sh, -1.0);
@@ -215,28 +372,6 @@ __global__ void __launch_bounds__(kRateThreads)
   }
 }
 
-// phi0 += dt * D^T (U_ext, W_ext)   scrap/parameter_interface/NGPSpheresLCP.cpp:751-756 (caller-layout velocities)
-template <bool SIX>
-__global__ void __launch_bounds__(256)
-    ext_correction_kernel(int64_t npairs, const int2* __restrict__ pairs, const double* __restrict__ normal,
-                          const double* __restrict__ arm_i, const double* __restrict__ arm_j,
-                          const double* __restrict__ U_ext, const double* __restrict__ W_ext, double dt,
-                          double* __restrict__ phi0) {
-  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (c >= npairs) return;
-  const int2 p = pairs[c];
-  V3 wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
-  const bool six = SIX && W_ext;
-  if (six) {
-    wi = ld3(W_ext, p.x), wj = ld3(W_ext, p.y);
-    ai = ld3(arm_i, c), aj = ld3(arm_j, c);
-  }
-  const V3 n = ld3(normal, c);
-  const double g = six ? contact_rate<true>(n, ld3(U_ext, p.x), ld3(U_ext, p.y), wi, wj, ai, aj)
-                       : contact_rate<false>(n, ld3(U_ext, p.x), ld3(U_ext, p.y), wi, wj, ai, aj);
-  phi0[c] += dt * g;
-}
-
 struct PinnedState {
   LcpState* h = nullptr;
   ~PinnedState() {
@@ -244,14 +379,20 @@ struct PinnedState {
   }
 };
 
+template <typename K>
+int resident_grid(K kernel, int threads) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+  return per_sm * kSMs;
+}
+
 }  // namespace
 
-int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const Incidence& inc,
-                            const mb200_lcp_params* params, const double* U_ext, const double* W_ext, double* phi0,
-                            double* gamma, double* F, double* T, double* U, double* W,
-                            mb200_collision_result* result_h) {
-  const int64_t n = op->n, C = op->npairs;
-  const bool six = op->arm_i != nullptr;
+int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& inc, const mb200_lcp_params* params,
+                    const double* U_ext, const double* W_ext, const double* gamma0, double* gamma_out,
+                    double* phi0_out, double* F, double* T, double* U, double* W, mb200_collision_result* result_h) {
+  const int64_t n = sys.n, C = sys.npairs;
+  const bool six = sys.six;
   const bool fixed = params->fixed_iters >= 0;
   const int it_cap = fixed ? params->fixed_iters : params->max_iters;
 
@@ -260,70 +401,75 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
 
   if (C == 0) {  // nothing to solve: zero force / velocity, residual identity of the max-reduction (-1)
     if (F) MB200_CUDA(cudaMemsetAsync(F, 0, 3 * n * sizeof(double), st));
-    if (U) MB200_CUDA(cudaMemsetAsync(U, 0, 3 * n * sizeof(double), st));
     if (six && T) MB200_CUDA(cudaMemsetAsync(T, 0, 3 * n * sizeof(double), st));
+    if (U) MB200_CUDA(cudaMemsetAsync(U, 0, 3 * n * sizeof(double), st));
     if (six && W) MB200_CUDA(cudaMemsetAsync(W, 0, 3 * n * sizeof(double), st));
     MB200_CUDA(cudaStreamSynchronize(st));
     if (result_h) *result_h = mb200_collision_result{-1.0, 0, 1, 0.0};
     return MB200_OK;
   }
 
-  const int64_t ntiles = (C + kTile - 1) / kTile;
-  const int rate_grid = static_cast<int>(ntiles < kSMs * 4 ? ntiles : kSMs * 4);
-  const int gam_grid = grid_for(C, 256, kSMs * 8);
-  const int body_grid = grid_for(n, 128);
+  static const int rate_cap6 = resident_grid(rate_pass_kernel<true, 1>, kRateThreads);
+  static const int rate_cap3 = resident_grid(rate_pass_kernel<false, 1>, kRateThreads);
+  const int rate_grid = grid_for(C, kRateThreads, six ? rate_cap6 : rate_cap3);
+  const int body_grid = grid_for(n, kBodiesPerCta);
+  const int cgrid = grid_for(C, 256);
 
-  Scratch<double> gamma_b, g_a, g_b, partials;
-  Scratch<D4> vel;
+  Scratch<double> partials;
+  Scratch<double2> s0, s1;
+  Scratch<D4> vel, mob;
   Scratch<LcpState> state;
-  MB200_TRY(gamma_b.alloc(C, st));
-  MB200_TRY(g_a.alloc(C, st));
-  MB200_TRY(g_b.alloc(C, st));
+  MB200_TRY(s0.alloc(C, st));
+  MB200_TRY(s1.alloc(C, st));
   MB200_TRY(partials.alloc(4 * static_cast<size_t>(rate_grid), st));
   MB200_TRY(vel.alloc(static_cast<size_t>(six ? 2 : 1) * n, st));
+  MB200_TRY(mob.alloc(n, st));
   MB200_TRY(state.alloc(1, st));
   MB200_CUDA(cudaMemsetAsync(state.p, 0, sizeof(LcpState), st));
 
   LcpArgs a;
   a.n = n, a.npairs = C;
-  a.pairs = reinterpret_cast<const int2*>(op->pairs);
-  a.normal = op->normal, a.arm_i = op->arm_i, a.arm_j = op->arm_j;
-  a.quat = op->quat, a.radius = op->radius, a.kind = op->kind;
+  a.pairs = sys.pairs, a.rec = sys.rec, a.mob = mob.p;
   a.inc_ptr = inc.ptr.p, a.inc_list = inc.list.p;
-  a.phi0 = phi0, a.vel = vel.p;
-  a.mu = op->viscosity, a.dt = op->dt, a.tol = params->tol;
+  a.vel = vel.p;
+  a.mu = sys.mu, a.dt = sys.dt, a.tol = params->tol;
   a.fixed = fixed ? 1 : 0, a.it_cap = it_cap;
   a.state = state.p, a.partials = partials.p;
 
-  if (U_ext) {
-    if (six)
-      ext_correction_kernel<true><<<grid_for(C, 256), 256, 0, st>>>(C, a.pairs, a.normal, a.arm_i, a.arm_j, U_ext,
-                                                                   W_ext, a.dt, phi0);
-    else
-      ext_correction_kernel<false><<<grid_for(C, 256), 256, 0, st>>>(C, a.pairs, a.normal, nullptr, nullptr, U_ext,
-                                                                    nullptr, a.dt, phi0);
+  {
+    StageScope ps(MB200_STAGE_LCP_SETUP, st);
+    mobility_records_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, sys.radius, sys.quat, sys.kind, mob.p);
     MB200_LAUNCHED();
+    init_state_kernel<<<cgrid, 256, 0, st>>>(C, gamma0, s0.p);
+    MB200_LAUNCHED();
+    if (U_ext) {
+      if (six)
+        ext_correction_kernel<true><<<cgrid, 256, 0, st>>>(C, sys.pairs, sys.rec, U_ext, W_ext, a.dt);
+      else
+        ext_correction_kernel<false><<<cgrid, 256, 0, st>>>(C, sys.pairs, sys.rec, U_ext, nullptr, a.dt);
+      MB200_LAUNCHED();
+    }
   }
 
-  // initial residual: g_a = D^T M D gamma_0
+  // initial residual: s1 = {gamma_0, g_0 = D^T M D gamma_0}
   {
     StageScope ps(MB200_STAGE_LCP_BODY, st);
     if (six)
-      body_pass_kernel<true, false><<<body_grid, 128, 0, st>>>(a, gamma, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+      body_pass_kernel<true, 0, false><<<body_grid, kBodyThreads, 0, st>>>(a, 0, s0.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
     else
-      body_pass_kernel<false, false><<<body_grid, 128, 0, st>>>(a, gamma, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+      body_pass_kernel<false, 0, false><<<body_grid, kBodyThreads, 0, st>>>(a, 0, s0.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
     MB200_LAUNCHED();
   }
   {
     StageScope ps(MB200_STAGE_LCP_RATE, st);
     if (six)
-      rate_pass_kernel<true, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, gamma, nullptr, nullptr, g_a.p);
+      rate_pass_kernel<true, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, 0, s0.p, s1.p);
     else
-      rate_pass_kernel<false, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, gamma, nullptr, nullptr, g_a.p);
+      rate_pass_kernel<false, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, 0, s0.p, s1.p);
     MB200_LAUNCHED();
   }
 
-  // iteration it: gamma_cur/g_cur are the B buffers when it is odd, the A buffers when even
+  // iteration `it` reads the previous state from s1 when it is odd (s0 when even) and writes the other buffer
   int it = 0;
   int batch = 4;
   LcpState hs;
@@ -336,44 +482,45 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
     while (it < stop) {
       ++it;
       const bool odd = it & 1;
-      double* gam_cur = odd ? gamma_b.p : gamma;
-      const double* gam_prev = odd ? gamma : gamma_b.p;
-      double* g_cur = odd ? g_b.p : g_a.p;
-      const double* g_prev = odd ? g_a.p : g_b.p;
-      {
-        StageScope ps(MB200_STAGE_LCP_GAMMA, st);
-        gamma_update_kernel<<<gam_grid, 256, 0, st>>>(C, gam_prev, phi0, g_prev, it == 1 ? 1 : 0, a.dt, state.p, gam_cur);
-        MB200_LAUNCHED();
-      }
+      const double2* prev = odd ? s1.p : s0.p;
+      double2* cur = odd ? s0.p : s1.p;
+      const int first = it == 1 ? 1 : 0;
       {
         StageScope ps(MB200_STAGE_LCP_BODY, st);
         if (six)
-          body_pass_kernel<true, false><<<body_grid, 128, 0, st>>>(a, gam_cur, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+          body_pass_kernel<true, 1, false><<<body_grid, kBodyThreads, 0, st>>>(a, first, prev, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
         else
-          body_pass_kernel<false, false><<<body_grid, 128, 0, st>>>(a, gam_cur, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+          body_pass_kernel<false, 1, false><<<body_grid, kBodyThreads, 0, st>>>(a, first, prev, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
         MB200_LAUNCHED();
       }
       {
         StageScope ps(MB200_STAGE_LCP_RATE, st);
         if (six)
-          rate_pass_kernel<true, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, gam_cur, gam_prev, g_prev, g_cur);
+          rate_pass_kernel<true, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, first, prev, cur);
         else
-          rate_pass_kernel<false, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, gam_cur, gam_prev, g_prev, g_cur);
+          rate_pass_kernel<false, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, first, prev, cur);
         MB200_LAUNCHED();
       }
     }
     if (batch < 32) batch *= 2;
   }
 
-  // final gamma lives in the B buffer when the last executed iteration is odd
+  // the state of the last executed iteration: written to s0 when it is odd, to s1 when even (or zero)
   const int it_final = hs.it;
-  if (it_final & 1) MB200_CUDA(cudaMemcpyAsync(gamma, gamma_b.p, C * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  const double2* fin = (it_final & 1) ? s0.p : s1.p;
   {
     StageScope ps(MB200_STAGE_LCP_BODY, st);
     if (six)
-      body_pass_kernel<true, true><<<body_grid, 128, 0, st>>>(a, gamma, F, T, U, W, nullptr, nullptr);
+      body_pass_kernel<true, 0, true><<<body_grid, kBodyThreads, 0, st>>>(a, 0, fin, F, T, U, W, nullptr, nullptr);
     else
-      body_pass_kernel<false, true><<<body_grid, 128, 0, st>>>(a, gamma, F, nullptr, U, nullptr, nullptr, nullptr);
+      body_pass_kernel<false, 0, true><<<body_grid, kBodyThreads, 0, st>>>(a, 0, fin, F, nullptr, U, nullptr, nullptr, nullptr);
+    MB200_LAUNCHED();
+  }
+  if (gamma_out || phi0_out) {
+    if (six)
+      unpack_contacts_kernel<true><<<cgrid, 256, 0, st>>>(C, sys.rec, fin, phi0_out, gamma_out);
+    else
+      unpack_contacts_kernel<false><<<cgrid, 256, 0, st>>>(C, sys.rec, fin, phi0_out, gamma_out);
     MB200_LAUNCHED();
   }
   MB200_CUDA(cudaMemcpyAsync(pinned.h, state.p, sizeof(LcpState), cudaMemcpyDeviceToHost, st));
@@ -383,9 +530,30 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
     result_h->max_abs_projected_sep = hs.res;
     result_h->ite_count = it_final;
     result_h->converged = (hs.res < params->tol) ? 1 : 0;
-    result_h->max_displacement = hs.vmax * op->dt;
+    result_h->max_displacement = hs.vmax * sys.dt;
   }
   return MB200_OK;
+}
+
+// Caller-layout front end: pack the contact arrays into records, solve, write phi0 / gamma back.
+int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const Incidence& inc,
+                            const mb200_lcp_params* params, const double* U_ext, const double* W_ext, double* phi0,
+                            double* gamma, double* F, double* T, double* U, double* W,
+                            mb200_collision_result* result_h) {
+  const int64_t C = op->npairs;
+  const bool six = op->arm_i != nullptr;
+  Scratch<D4> rec;
+  MB200_TRY(rec.alloc(static_cast<size_t>(six ? 3 : 1) * (C > 0 ? C : 1), st));
+  const int2* pairs = reinterpret_cast<const int2*>(op->pairs);
+  if (C > 0) {
+    if (six)
+      pack_contacts_kernel<true><<<grid_for(C, 256), 256, 0, st>>>(C, pairs, op->normal, op->arm_i, op->arm_j, phi0, rec.p);
+    else
+      pack_contacts_kernel<false><<<grid_for(C, 256), 256, 0, st>>>(C, pairs, op->normal, nullptr, nullptr, phi0, rec.p);
+    MB200_LAUNCHED();
+  }
+  RecordSystem sys{op->n, C, six, pairs, rec.p, op->quat, op->radius, op->kind, op->viscosity, op->dt};
+  return resolve_records(st, sys, inc, params, U_ext, W_ext, gamma, gamma, U_ext ? phi0 : nullptr, F, T, U, W, result_h);
 }
 
 }  // namespace mb200

@@ -199,13 +199,7 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
         Wext_s = h->vec_b.p;
       }
     }
-    MB200_TRY(h->phi0.reserve(C + 1));
-    MB200_TRY(h->normal.reserve(3 * C + 1));
-    MB200_TRY(h->gamma.reserve(C + 1));
-    if (rods) {
-      MB200_TRY(h->arm_i.reserve(3 * C + 1));
-      MB200_TRY(h->arm_j.reserve(3 * C + 1));
-    }
+    MB200_TRY(h->rec.reserve(static_cast<size_t>(rods ? 3 : 1) * C + 1));
     {
       StageScope ps(MB200_STAGE_PACK, st);
       MB200_TRY(pack_bodies(st, bodies, reinterpret_cast<const int32_t*>(h->perm.p), h->b0.p, rods ? h->b1.p : nullptr));
@@ -217,8 +211,7 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
     }
     {  // narrow phase on the links
       StageScope ps(MB200_STAGE_NARROW, st);
-      MB200_TRY(narrow_phase_records(st, C, h->pairs.p, h->b0.p, rods ? h->b1.p : nullptr, h->phi0.p, h->normal.p,
-                                     rods ? h->arm_i.p : nullptr, rods ? h->arm_j.p : nullptr));
+      MB200_TRY(narrow_phase_to_records(st, C, h->pairs.p, h->b0.p, rods ? h->b1.p : nullptr, rods, h->rec.p));
     }
     // LCP
     MB200_TRY(h->vec_c.reserve(3 * n));
@@ -227,19 +220,14 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
       MB200_TRY(h->vec_e.reserve(3 * n));
       MB200_TRY(h->vec_f.reserve(3 * n));
     }
-    if (C > 0) MB200_CUDA(cudaMemsetAsync(h->gamma.p, 0, C * sizeof(double), st));
-    mb200_contact_op op;
-    op.n = n, op.npairs = C, op.pairs = h->pairs.p, op.normal = h->normal.p;
-    op.arm_i = rods ? h->arm_i.p : nullptr, op.arm_j = rods ? h->arm_j.p : nullptr;
-    op.quat = rods ? h->quat_s.p : nullptr, op.radius = h->radius_s.p, op.kind = rods ? h->kind_s.p : nullptr;
-    op.viscosity = params->viscosity, op.dt = params->dt;
+    RecordSystem sys{n, C, rods, reinterpret_cast<const int2*>(h->pairs.p), h->rec.p, rods ? h->quat_s.p : nullptr,
+                     h->radius_s.p, rods ? h->kind_s.p : nullptr, params->viscosity, params->dt};
     mb200_lcp_params lp{params->tol, params->max_iters, params->fixed_iters};
     double* F_s = h->vec_c.p;
     double* U_s = h->vec_d.p;
     double* T_s = rods ? h->vec_e.p : nullptr;
     double* W_s = rods ? h->vec_f.p : nullptr;
-    MB200_TRY(resolve_collisions_impl(st, &op, h->inc, &lp, Uext_s, Wext_s, h->phi0.p, h->gamma.p, F_s, T_s, U_s, W_s,
-                                      &res));
+    MB200_TRY(resolve_records(st, sys, h->inc, &lp, Uext_s, Wext_s, nullptr, nullptr, nullptr, F_s, T_s, U_s, W_s, &res));
     if (params->throw_on_max_iters && params->fixed_iters < 0 && res.ite_count == params->max_iters && !res.converged) {
       set_error("Collision resolution did not converge!");  // scrap/lcp_spheres/NGPSpheresLCP.cpp:745-747
       if (stats_h) *stats_h = mb200_step_stats{res, C, rebuilt, static_cast<int32_t>(g_launches.load() - launches0)};
