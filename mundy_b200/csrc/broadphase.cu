@@ -110,16 +110,34 @@ __global__ void __launch_bounds__(256) cell_ranges_kernel(int64_t n, const uint3
   if (k == n - 1 || keys[k + 1] != key) cell_range[key].y = static_cast<int>(k + 1);
 }
 
-// One warp per body i (Morton order). FILL = false: counts[i] = number of kept pairs (i, j>i).
-// FILL = true: writes them at pairs[rowptr[i] ...] in ascending j.
+// One warp per body i (Morton order).
+//   FILL = false: counts[i] = number of kept pairs (i, j>i); the first `slot_cap` of them are also cached in
+//                 slots[i * slot_cap ...] so that the fill pass does not have to search again.
+//   FILL = true : writes the pairs at pairs[rowptr[i] ...] in ascending j: copied from the slots when they all fit,
+//                 found again otherwise.
+// The candidates of the <= 27 neighbour cells with key >= own key are walked as ONE flattened index range in
+// ascending key order (= ascending j): 64 candidates per trip, both 256-bit record loads of a lane issued before the
+// first test, exact fp64 predicate, warp ballot + popc compaction.
 template <bool FILL, bool FILTER>
 __global__ void __launch_bounds__(256)
     find_pairs_kernel(int64_t n, const D4* __restrict__ sr, const D4* __restrict__ b0, const D4* __restrict__ b1,
                       const uint32_t* __restrict__ perm, const int2* __restrict__ cell_range, GridParams gp,
-                      double cutoff, uint32_t* __restrict__ counts, const int64_t* __restrict__ rowptr, int2* __restrict__ pairs) {
+                      double cutoff, uint32_t* __restrict__ counts, const int64_t* __restrict__ rowptr,
+                      int2* __restrict__ pairs, int32_t* __restrict__ slots, int slot_cap) {
   const int lane = threadIdx.x & 31;
+  const int wib = threadIdx.x >> 5;
   const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   if (i >= n) return;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  int64_t out = FILL ? rowptr[i] : 0;
+  if (FILL) {
+    const int cnt = static_cast<int>(rowptr[i + 1] - out);
+    if (cnt <= slot_cap) {  // everything was cached by the count pass
+      for (int k = lane; k < cnt; k += 32)
+        pairs[out + k] = make_int2(static_cast<int>(i), slots[i * slot_cap + k]);
+      return;
+    }
+  }
   const D4 si = ldg256(sr + i);
   D4 b0i{0, 0, 0, 0}, b1i{0, 0, 0, 0};
   uint32_t pi = 0;
@@ -134,7 +152,7 @@ __global__ void __launch_bounds__(256)
   const uint32_t my_key = morton3(cx, cy, cz);
   // lane l < 27 owns neighbour cell l
   uint32_t nkey = 0xffffffffu;
-  int beg = 0, end = 0;
+  int beg = 0, len = 0;
   if (lane < 27) {
     const int x = cx + (lane % 3) - 1, y = cy + ((lane / 3) % 3) - 1, z = cz + (lane / 9) - 1;
     if (x >= 0 && y >= 0 && z >= 0 && x < gp.nc[0] && y < gp.nc[1] && z < gp.nc[2]) {
@@ -142,45 +160,101 @@ __global__ void __launch_bounds__(256)
       if (k >= my_key) {  // bodies with a smaller key have a smaller index: never j > i
         const int2 r = __ldg(cell_range + k);
         beg = (k == my_key) ? static_cast<int>(i) + 1 : r.x;
-        end = r.y;
-        if (end > beg) nkey = k;
+        len = r.y - beg;
+        if (len > 0) nkey = k; else len = 0;
       }
     }
   }
   const bool valid = nkey != 0xffffffffu;
-  int rank = 0;  // ascending-key rank among the valid cells
+  // ascending-key rank among the valid cells and the number of candidates in front of this cell
+  int rank = 0, pre = 0;
 #pragma unroll
   for (int m = 0; m < 27; ++m) {
     const uint32_t km = __shfl_sync(0xffffffffu, nkey, m);
-    rank += (km < nkey) ? 1 : 0;
-  }
-  const int nvalid = __popc(__ballot_sync(0xffffffffu, valid));
-  const uint32_t lt_mask = (1u << lane) - 1u;
-  int64_t out = FILL ? rowptr[i] : 0;
-  uint32_t total = 0;
-  for (int r = 0; r < nvalid; ++r) {
-    const int src = __ffs(__ballot_sync(0xffffffffu, valid && rank == r)) - 1;
-    const int cbeg = __shfl_sync(0xffffffffu, beg, src);
-    const int cend = __shfl_sync(0xffffffffu, end, src);
-    for (int j0 = cbeg; j0 < cend; j0 += 32) {
-      const int j = j0 + lane;
-      bool keep = false;
-      if (j < cend) {
-        keep = is_candidate(si, ldg256(sr + j));
-        if (FILTER && keep) {
-          // evaluate in the caller's (i<j) order so that the decision is bit-identical to the reference order
-          const D4 b0j = ldg256(b0 + j), b1j = ldg256(b1 + j);
-          const PairGeom g = (pi < perm[j]) ? pair_geometry<true>(b0i, b1i, b0j, b1j)
-                                            : pair_geometry<true>(b0j, b1j, b0i, b1i);
-          keep = g.sep <= cutoff;
-        }
-      }
-      const uint32_t m = __ballot_sync(0xffffffffu, keep);
-      if (FILL && keep) pairs[out + __popc(m & lt_mask)] = make_int2(static_cast<int>(i), j);
-      out += __popc(m);
-      total += __popc(m);
+    const int lm = __shfl_sync(0xffffffffu, len, m);
+    if (km < nkey) {
+      rank += 1;
+      pre += lm;
     }
   }
+  const int nvalid = __popc(__ballot_sync(0xffffffffu, valid));
+  __shared__ int s_pre[8][28], s_beg[8][28];
+  __shared__ int s_queue[FILTER ? 8 : 1][FILTER ? 96 : 1];
+  if (valid) {
+    s_pre[wib][rank] = pre;
+    s_beg[wib][rank] = beg;
+  }
+  int total_cand = valid ? pre + len : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) total_cand = max(total_cand, __shfl_xor_sync(0xffffffffu, total_cand, o));
+  __syncwarp();
+  const int* wpre = s_pre[wib];
+  const int* wbeg = s_beg[wib];
+  auto candidate = [&](int t) {  // flattened index -> body index
+    int lo = 0, hi = nvalid - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (wpre[mid] <= t) lo = mid; else hi = mid - 1;
+    }
+    return wbeg[lo] + (t - wpre[lo]);
+  };
+
+  uint32_t total = 0;
+  // With the shape filter the survivors of the sphere test (about 1 in 10) are queued per warp and the expensive
+  // shape distance runs on dense batches of 32, in queue order (= ascending j), instead of on a few divergent lanes.
+  int* q = s_queue[FILTER ? wib : 0];
+  int qn = 0;
+  auto emit = [&](bool keep, int j) {
+    const uint32_t m = __ballot_sync(0xffffffffu, keep);
+    if (keep) {
+      const int pos = static_cast<int>(total) + __popc(m & lt_mask);
+      if (FILL) pairs[out + pos] = make_int2(static_cast<int>(i), j);
+      else if (pos < slot_cap) slots[i * slot_cap + pos] = j;
+    }
+    total += __popc(m);
+  };
+  auto evaluate = [&](int take) {
+    const int j = (lane < take) ? q[lane] : -1;
+    bool keep = false;
+    if (j >= 0) {
+      // evaluate in the caller's (i<j) order so that the decision is bit-identical to the reference order
+      const D4 b0j = ldg256(b0 + j), b1j = ldg256(b1 + j);
+      const PairGeom g = (pi < perm[j]) ? pair_geometry<true>(b0i, b1i, b0j, b1j)
+                                        : pair_geometry<true>(b0j, b1j, b0i, b1i);
+      keep = g.sep <= cutoff;
+    }
+    emit(keep, j);
+    // the qn - take < 64 remaining entries move to the front
+    const int r0 = (lane + take < qn) ? q[lane + take] : 0;
+    const int r1 = (lane + 32 + take < qn) ? q[lane + 32 + take] : 0;
+    __syncwarp();
+    q[lane] = r0;
+    q[lane + 32] = r1;
+    __syncwarp();
+    qn -= take;
+  };
+  for (int t0 = 0; t0 < total_cand; t0 += 64) {
+    const int ta = t0 + lane, tb = t0 + 32 + lane;
+    const int ja = (ta < total_cand) ? candidate(ta) : -1;
+    const int jb = (tb < total_cand) ? candidate(tb) : -1;
+    D4 sa{0, 0, 0, 0}, sb{0, 0, 0, 0};
+    if (ja >= 0) sa = ldg256(sr + ja);
+    if (jb >= 0) sb = ldg256(sr + jb);
+    const bool ka = (ja >= 0) && is_candidate(si, sa);
+    const bool kb = (jb >= 0) && is_candidate(si, sb);
+    if (FILTER) {
+      const uint32_t ma = __ballot_sync(0xffffffffu, ka), mb = __ballot_sync(0xffffffffu, kb);
+      if (ka) q[qn + __popc(ma & lt_mask)] = ja;
+      if (kb) q[qn + __popc(ma) + __popc(mb & lt_mask)] = jb;
+      qn += __popc(ma) + __popc(mb);
+      __syncwarp();
+      while (qn >= 32) evaluate(32);
+    } else {
+      emit(ka, ja);
+      emit(kb, jb);
+    }
+  }
+  if (FILTER && qn > 0) evaluate(qn);
   if (!FILL && lane == 0) counts[i] = total;
 }
 
@@ -322,16 +396,19 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   // 4. count -> scan -> fill
   Scratch<uint32_t> counts;
   Scratch<int64_t> rowptr;
+  Scratch<int32_t> slots;
+  const int slot_cap = filter ? 16 : 48;  // kept pairs cached per body by the count pass (more => recomputed by the fill pass)
+  MB200_TRY(slots.alloc(static_cast<size_t>(n) * slot_cap, st));
   MB200_TRY(counts.alloc(n, st));
   MB200_TRY(rowptr.alloc(n + 1, st));
   const double cutoff = 2.0 * h->buffer;
   const int pgrid = grid_for(n * 32, 256);
   if (filter)
     find_pairs_kernel<false, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
-                                                         counts.p, nullptr, nullptr);
+                                                         counts.p, nullptr, nullptr, slots.p, slot_cap);
   else
     find_pairs_kernel<false, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
-                                                          cutoff, counts.p, nullptr, nullptr);
+                                                          cutoff, counts.p, nullptr, nullptr, slots.p, slot_cap);
   MB200_LAUNCHED();
   MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, rowptr.p));
   int64_t total = 0;
@@ -347,10 +424,10 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
     int2* out = reinterpret_cast<int2*>(h->pairs.p);
     if (filter)
       find_pairs_kernel<true, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
-                                                          nullptr, rowptr.p, out);
+                                                          nullptr, rowptr.p, out, slots.p, slot_cap);
     else
       find_pairs_kernel<true, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
-                                                           cutoff, nullptr, rowptr.p, out);
+                                                           cutoff, nullptr, rowptr.p, out, slots.p, slot_cap);
     MB200_LAUNCHED();
   }
   // 5. body-major incidence lists for the contact operator
