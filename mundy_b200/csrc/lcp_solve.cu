@@ -156,8 +156,22 @@ constexpr int kBodiesPerCta = 64;
 constexpr int kCap = 512;  // incidence entries staged per round (avg ~6.4 per rod at cfg3 => one round per CTA)
 constexpr int kUnroll = 4;  // entries in flight per thread
 
+__device__ inline void cp_async4(void* smem_dst, const void* gsrc) {
+  const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ inline void cp_async8(void* smem_dst, const void* gsrc) {
+  const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ inline void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // MODE 0: gamma is read from the state (initial pass and final pass). MODE 1: gamma re-derived from the previous state.
 // FINAL: also writes F,T,U,W in the solver's body order and reduces max |U| into state->vmax (single launch at the end).
+// Persistent CTAs walk blocks of kBodiesPerCta bodies. The chain of dependent loads of a block (incidence pointers ->
+// incidence list -> contact records) is software-pipelined across blocks with cp.async: while block k is processed,
+// the list of block k + G and the pointers of block k + 2G stream into shared memory, so that only the record gathers
+// remain on the critical path.
 template <bool SIX, int MODE, bool FINAL>
 __global__ void __launch_bounds__(kBodyThreads)
     body_pass_kernel(LcpArgs a, int first, const double2* __restrict__ st_prev, double* __restrict__ F,
@@ -167,101 +181,136 @@ __global__ void __launch_bounds__(kBodyThreads)
   constexpr int NC = SIX ? 6 : 3;
   __shared__ double s_w[NC][kCap];
   __shared__ double sh[33];
+  __shared__ __align__(8) int64_t s_ptr[3][kBodiesPerCta + 1];
+  __shared__ uint32_t s_list[2][kCap];
   const double alpha = (MODE == 1) ? a.state->alpha : 0.0;
   const int t = threadIdx.x;
-  const int64_t b0 = static_cast<int64_t>(blockIdx.x) * kBodiesPerCta;
-  const int nb = static_cast<int>(min(static_cast<int64_t>(kBodiesPerCta), a.n - b0));
-  __shared__ int64_t s_ptr[kBodiesPerCta + 1];
-  if (t <= nb) s_ptr[t] = a.inc_ptr[b0 + t];
-  D4 mr{0.0, 0.0, 1.0, -1.0};
-  if (t < nb) mr = ldg256(a.mob + b0 + t);  // needed only at the end: issued now to overlap with everything else
-  __syncthreads();
-  const int64_t e_begin = s_ptr[0], e_end = s_ptr[nb];
-  int64_t my_beg = 0, my_end = 0;
-  if (t < nb) my_beg = s_ptr[t], my_end = s_ptr[t + 1];
-  double acc[NC];
-#pragma unroll
-  for (int k = 0; k < NC; ++k) acc[k] = 0.0;
+  const int64_t nblk = (a.n + kBodiesPerCta - 1) / kBodiesPerCta;
+  const int64_t G = gridDim.x;
+  int64_t blk = blockIdx.x;
+  double speed = 0.0;
 
-  for (int64_t rb = e_begin; rb < e_end; rb += kCap) {
-    const int cnt = static_cast<int>(min(static_cast<int64_t>(kCap), e_end - rb));
-    // phase 1: every thread forms the wrench of up to kUnroll (contact, side) entries; the loads of all of them are
-    // issued before the first use (independent gathers: memory-level parallelism instead of occupancy)
-    for (int k0 = 0; k0 < cnt; k0 += kBodyThreads * kUnroll) {
-      uint32_t e[kUnroll];
-      double2 sp[kUnroll];
-      D4 r0[kUnroll], ra[kUnroll];
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int k = k0 + u * kBodyThreads + t;
-        e[u] = (k < cnt) ? __ldg(a.inc_list + rb + k) : 0xffffffffu;
-      }
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        if (e[u] != 0xffffffffu) {
-          const int64_t c = e[u] >> 1;
-          sp[u] = ldg128(st_prev + c);
-          r0[u] = ldg256(a.rec + (SIX ? 3 * c : c));
-          if (SIX) ra[u] = ldg256(a.rec + 3 * c + 1 + (e[u] & 1u));
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        if (e[u] != 0xffffffffu) {
-          const int k = k0 + u * kBodyThreads + t;
-          const int is_j = e[u] & 1u;
-          const double g = gamma_of<MODE>(sp[u], r0[u].w, alpha, a.dt, first);
-          // n_I = n, n_J = -n: F += -gamma n_side, T += -gamma (r_side x n_side)   (scrap/UnitTestMundy.cpp:652-674)
-          const double mx = is_j ? -r0[u].x : r0[u].x, my = is_j ? -r0[u].y : r0[u].y, mz = is_j ? -r0[u].z : r0[u].z;
-          s_w[0][k] = -g * mx;
-          s_w[1][k] = -g * my;
-          s_w[2][k] = -g * mz;
-          if (SIX) {
-            s_w[3][k] = -g * (ra[u].y * mz - ra[u].z * my);
-            s_w[4][k] = -g * (ra[u].z * mx - ra[u].x * mz);
-            s_w[5][k] = -g * (ra[u].x * my - ra[u].y * mx);
-          }
-        }
-      }
-    }
+  auto bodies_in = [&](int64_t k) {
+    return static_cast<int>(min(static_cast<int64_t>(kBodiesPerCta), a.n - k * kBodiesPerCta));
+  };
+  auto fetch_ptrs = [&](int64_t k, int buf) {  // async: inc_ptr[k * B .. k * B + nb]
+    if (k < nblk && t <= bodies_in(k)) cp_async8(&s_ptr[buf][t], a.inc_ptr + k * kBodiesPerCta + t);
+  };
+  auto fetch_list = [&](int64_t k, int pbuf, int lbuf) {  // async: first kCap incidence entries of block k
+    if (k >= nblk) return;
+    const int64_t eb = s_ptr[pbuf][0];
+    const int cnt = static_cast<int>(min(static_cast<int64_t>(kCap), s_ptr[pbuf][bodies_in(k)] - eb));
+    for (int j = t; j < cnt; j += kBodyThreads) cp_async4(&s_list[lbuf][j], a.inc_list + eb + j);
+  };
+
+  if (blk < nblk) {  // prologue: pointers of the first two blocks, list of the first
+    fetch_ptrs(blk, 0);
+    fetch_ptrs(blk + G, 1);
+    cp_async_wait_all();
     __syncthreads();
-    // phase 2: one thread per body adds its entries in ascending (contact, side) order
-    if (t < nb) {
-      const int lo = static_cast<int>(max(my_beg, rb) - rb);
-      const int hi = static_cast<int>(min(my_end, rb + cnt) - rb);
-      for (int k = lo; k < hi; ++k) {
-#pragma unroll
-        for (int j = 0; j < NC; ++j) acc[j] += s_w[j][k];
-      }
-    }
+    fetch_list(blk, 0, 0);
+    cp_async_wait_all();
     __syncthreads();
   }
 
-  double speed = 0.0;
-  if (t < nb) {
-    const int64_t b = b0 + t;
-    const bool rod = SIX && mr.w > 0.0;
-    const Mob m = mobility_of(fabs(mr.w), a.mu);
-    const V3 f{acc[0], acc[1], acc[2]};
-    const V3 tq = SIX ? V3{acc[3], acc[4], acc[5]} : V3{0.0, 0.0, 0.0};
-    V3 u, w;
-    body_mobility_axis(m, rod, V3{mr.x, mr.y, mr.z}, f, tq, u, w);
-    if (!FINAL) {
-      if (SIX) {
-        st256(a.vel + 2 * b, D4{u.x, u.y, u.z, 0.0});
-        st256(a.vel + 2 * b + 1, D4{w.x, w.y, w.z, 0.0});
-      } else {
-        st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
+  for (int stage = 0; blk < nblk; blk += G, ++stage) {
+    const int pcur = stage % 3, pnext = (stage + 1) % 3, pnn = (stage + 2) % 3, lcur = stage & 1;
+    fetch_ptrs(blk + 2 * G, pnn);
+    fetch_list(blk + G, pnext, lcur ^ 1);
+
+    const int64_t b0 = blk * kBodiesPerCta;
+    const int nb = bodies_in(blk);
+    D4 mr{0.0, 0.0, 1.0, -1.0};
+    if (t < nb) mr = ldg256(a.mob + b0 + t);  // needed only at the end: issued now to overlap with the gathers
+    const int64_t e_begin = s_ptr[pcur][0], e_end = s_ptr[pcur][nb];
+    int64_t my_beg = 0, my_end = 0;
+    if (t < nb) my_beg = s_ptr[pcur][t], my_end = s_ptr[pcur][t + 1];
+    double acc[NC];
+#pragma unroll
+    for (int k = 0; k < NC; ++k) acc[k] = 0.0;
+
+    for (int64_t rb = e_begin; rb < e_end; rb += kCap) {
+      const int cnt = static_cast<int>(min(static_cast<int64_t>(kCap), e_end - rb));
+      const bool staged = rb == e_begin;  // later rounds (more than kCap entries in the block) read the list directly
+      // phase 1: every thread forms the wrench of up to kUnroll (contact, side) entries; the loads of all of them are
+      // issued before the first use (independent gathers: memory-level parallelism instead of occupancy)
+      for (int k0 = 0; k0 < cnt; k0 += kBodyThreads * kUnroll) {
+        uint32_t e[kUnroll];
+        double2 sp[kUnroll];
+        D4 r0[kUnroll], ra[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const int k = k0 + u * kBodyThreads + t;
+          e[u] = (k < cnt) ? (staged ? s_list[lcur][k] : __ldg(a.inc_list + rb + k)) : 0xffffffffu;
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          if (e[u] != 0xffffffffu) {
+            const int64_t c = e[u] >> 1;
+            sp[u] = ldg128(st_prev + c);
+            r0[u] = ldg256(a.rec + (SIX ? 3 * c : c));
+            if (SIX) ra[u] = ldg256(a.rec + 3 * c + 1 + (e[u] & 1u));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          if (e[u] != 0xffffffffu) {
+            const int k = k0 + u * kBodyThreads + t;
+            const int is_j = e[u] & 1u;
+            const double g = gamma_of<MODE>(sp[u], r0[u].w, alpha, a.dt, first);
+            // n_I = n, n_J = -n: F += -gamma n_side, T += -gamma (r_side x n_side)  (scrap/UnitTestMundy.cpp:652-674)
+            const double mx = is_j ? -r0[u].x : r0[u].x, my = is_j ? -r0[u].y : r0[u].y, mz = is_j ? -r0[u].z : r0[u].z;
+            s_w[0][k] = -g * mx;
+            s_w[1][k] = -g * my;
+            s_w[2][k] = -g * mz;
+            if (SIX) {
+              s_w[3][k] = -g * (ra[u].y * mz - ra[u].z * my);
+              s_w[4][k] = -g * (ra[u].z * mx - ra[u].x * mz);
+              s_w[5][k] = -g * (ra[u].x * my - ra[u].y * mx);
+            }
+          }
+        }
       }
-    } else {
-      speed = sqrt(u.x * u.x + u.y * u.y + u.z * u.z);  // KokkosLCP.cpp:861-872 (collision velocity only)
-      if (F) st3(F, b, f);
-      if (SIX && T) st3(T, b, tq);
-      if (U_ext) u = u + ld3(U_ext, b);  // U += U_col on top of the external velocity (NGPSpheresLCP.cpp:867-877)
-      if (SIX && W_ext) w = w + ld3(W_ext, b);
-      if (U) st3(U, b, u);
-      if (SIX && W) st3(W, b, w);
+      __syncthreads();
+      // phase 2: one thread per body adds its entries in ascending (contact, side) order
+      if (t < nb) {
+        const int lo = static_cast<int>(max(my_beg, rb) - rb);
+        const int hi = static_cast<int>(min(my_end, rb + cnt) - rb);
+        for (int k = lo; k < hi; ++k) {
+#pragma unroll
+          for (int j = 0; j < NC; ++j) acc[j] += s_w[j][k];
+        }
+      }
+      __syncthreads();
     }
+
+    if (t < nb) {
+      const int64_t b = b0 + t;
+      const bool rod = SIX && mr.w > 0.0;
+      const Mob m = mobility_of(fabs(mr.w), a.mu);
+      const V3 f{acc[0], acc[1], acc[2]};
+      const V3 tq = SIX ? V3{acc[3], acc[4], acc[5]} : V3{0.0, 0.0, 0.0};
+      V3 u, w;
+      body_mobility_axis(m, rod, V3{mr.x, mr.y, mr.z}, f, tq, u, w);
+      if (!FINAL) {
+        if (SIX) {
+          st256(a.vel + 2 * b, D4{u.x, u.y, u.z, 0.0});
+          st256(a.vel + 2 * b + 1, D4{w.x, w.y, w.z, 0.0});
+        } else {
+          st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
+        }
+      } else {
+        speed = fmax(speed, sqrt(u.x * u.x + u.y * u.y + u.z * u.z));  // KokkosLCP.cpp:861-872 (collision velocity)
+        if (F) st3(F, b, f);
+        if (SIX && T) st3(T, b, tq);
+        if (U_ext) u = u + ld3(U_ext, b);  // U += U_col on top of the external velocity (NGPSpheresLCP.cpp:867-877)
+        if (SIX && W_ext) w = w + ld3(W_ext, b);
+        if (U) st3(U, b, u);
+        if (SIX && W) st3(W, b, w);
+      }
+    }
+    cp_async_wait_all();  // next block's list and the block after's pointers have landed
+    __syncthreads();
   }
   if (FINAL) {
     const double m = block_max(speed, sh, 0.0);
@@ -412,7 +461,9 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   static const int rate_cap6 = resident_grid(rate_pass_kernel<true, 1>, kRateThreads);
   static const int rate_cap3 = resident_grid(rate_pass_kernel<false, 1>, kRateThreads);
   const int rate_grid = grid_for(C, kRateThreads, six ? rate_cap6 : rate_cap3);
-  const int body_grid = grid_for(n, kBodiesPerCta);
+  static const int body_cap6 = resident_grid(body_pass_kernel<true, 1, false>, kBodyThreads);
+  static const int body_cap3 = resident_grid(body_pass_kernel<false, 1, false>, kBodyThreads);
+  const int body_grid = grid_for(n, kBodiesPerCta, six ? body_cap6 : body_cap3);
   const int cgrid = grid_for(C, 256);
 
   Scratch<double> partials;
