@@ -3,7 +3,7 @@
 // include/ may import, link or call it.
 //
 // Parity status: the arithmetic leaves (AABB, distance, quaternion ops, math::convex PGD) are PINNED bit-for-bit against
-// the reference's own headers compiled into oracle/_ref/libmundy_ref.so (tests/test_oracle_vs_reference.py) and against the
+// the reference's own headers compiled into oracle/_ref/libmundy_ref.so (tests/test_oracle_goldens.py::test_oracle_vs_live_reference_random and the stored outputs tests/golden/ref_outputs.npz) and against the
 // reference's golden vectors (tests/test_oracle_goldens.py). The driver loop (BBPGD, D / D^T / M kernels) and the
 // 6-DOF rod Jacobian are restated from scrap/ programs that cannot be linked here (STK/ArborX absent) and are checked
 // through their analytical properties. The neighbour SEARCH restates a predicate whose implementation lives in
