@@ -53,6 +53,14 @@ const char* mb200_last_error_string(void);
 /* Number of visible CUDA devices (0 when none / no driver). Host-only query. */
 int mb200_device_count(void);
 
+/* Device-memory helpers for hosts that do not link the CUDA runtime themselves (FFI callers, the C++ veneer's
+ * single-object convenience overloads). Thin wrappers over cudaMalloc / cudaFree / cudaMemcpyAsync / stream sync. */
+int mb200_device_alloc(void** out, int64_t bytes);
+int mb200_device_free(void* ptr);
+int mb200_copy_to_device(mb200_stream stream, void* dst, const void* src_h, int64_t bytes);
+int mb200_copy_to_host(mb200_stream stream, void* dst_h, const void* src, int64_t bytes);
+int mb200_stream_synchronize(mb200_stream stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * A. geom::compute_aabb, batched.   mundy/geom/src/mundy_geom/compute_aabb.hpp
  * ------------------------------------------------------------------------------------------------------------- */

@@ -1,0 +1,219 @@
+// mundy_b200/geom.hpp — the geom:: seam of the reference on top of the C-ABI.
+//
+// Reference signatures kept (all under mundy/geom/src/mundy_geom/):
+//   AABB<Scalar> compute_aabb(const Sphere&)                 compute_aabb.hpp:72-80
+//   AABB<Scalar> compute_aabb(const Spherocylinder&)         compute_aabb.hpp:106-127   (axis = q (x) z_hat)
+//   AABB<Scalar> compute_aabb(const SpherocylinderSegment&)  compute_aabb.hpp:130-143
+//   Scalar distance([SharedNormalSigned,] Sphere, Sphere[, sep])                         distance/SphereSphere.hpp:54-76
+//   Scalar distance([tag,] LineSegment, LineSegment, cp1, cp2, s, t, sep)                distance/LineSegmentLineSegment.hpp:189-318
+//   Scalar distance([tag,] Point, LineSegment, cp, t, sep)                               distance/PointLineSegment.hpp:128-172
+//   Scalar distance([tag,] LineSegment, Sphere, cp, t, sep)                              distance/LineSegmentSphere.hpp:86-99
+// Value types mirror primitives/{Point,Sphere,Spherocylinder,SpherocylinderSegment,LineSegment,AABB}.hpp accessors.
+// The single-object overloads run on the device through a one-element batch (they exist so that code and tests written
+// against the reference compile unchanged); bulk work should use the *_batch functions, which take device arrays in the
+// reference's layouts and are asynchronous on `stream`.
+#ifndef MUNDY_B200_GEOM_HPP_
+#define MUNDY_B200_GEOM_HPP_
+
+#include <array>
+
+#include "core.hpp"
+
+namespace mundy_b200 {
+namespace geom {
+
+struct Vector3 {
+  double v[3]{0, 0, 0};
+  Vector3() = default;
+  Vector3(double x, double y, double z) : v{x, y, z} {}
+  double& operator[](int i) { return v[i]; }
+  const double& operator[](int i) const { return v[i]; }
+};
+using Point = Vector3;
+
+struct Quaternion {  // (w, x, y, z), mundy/math/src/mundy_math/Quaternion.hpp
+  double q[4]{1, 0, 0, 0};
+  Quaternion() = default;
+  Quaternion(double w, double x, double y, double z) : q{w, x, y, z} {}
+  double w() const { return q[0]; }
+  const double* vector() const { return q + 1; }
+};
+
+struct SharedNormalSigned {};  // distance/Types.hpp:30-39 (the default distance type)
+
+class AABB {  // primitives/AABB.hpp: flat index 0..5 = min xyz, max xyz (:199-202)
+ public:
+  AABB() = default;
+  AABB(const Point& lo, const Point& hi) : c_{lo[0], lo[1], lo[2], hi[0], hi[1], hi[2]} {}
+  double operator[](int i) const { return c_[i]; }
+  double& operator[](int i) { return c_[i]; }
+  Point min_corner() const { return {c_[0], c_[1], c_[2]}; }
+  Point max_corner() const { return {c_[3], c_[4], c_[5]}; }
+  double x_min() const { return c_[0]; }
+  double y_min() const { return c_[1]; }
+  double z_min() const { return c_[2]; }
+  double x_max() const { return c_[3]; }
+  double y_max() const { return c_[4]; }
+  double z_max() const { return c_[5]; }
+  double* data() { return c_.data(); }
+
+ private:
+  std::array<double, 6> c_{0, 0, 0, 0, 0, 0};
+};
+/// Closed-interval overlap test, touching counts (primitives/AABB.hpp:419-431). Pure predicate on two values.
+inline bool intersects(const AABB& a, const AABB& b) {
+  for (int d = 0; d < 3; ++d)
+    if (a[3 + d] < b[d] || b[3 + d] < a[d]) return false;
+  return true;
+}
+
+class Sphere {
+ public:
+  Sphere(const Point& c, double r) : c_(c), r_(r) {}
+  const Point& center() const { return c_; }
+  double radius() const { return r_; }
+
+ private:
+  Point c_;
+  double r_;
+};
+class Spherocylinder {
+ public:
+  Spherocylinder(const Point& c, const Quaternion& q, double r, double len) : c_(c), q_(q), r_(r), len_(len) {}
+  const Point& center() const { return c_; }
+  const Quaternion& orientation() const { return q_; }
+  double radius() const { return r_; }
+  double length() const { return len_; }
+
+ private:
+  Point c_;
+  Quaternion q_;
+  double r_, len_;
+};
+class LineSegment {
+ public:
+  LineSegment(const Point& a, const Point& b) : a_(a), b_(b) {}
+  const Point& start() const { return a_; }
+  const Point& end() const { return b_; }
+
+ private:
+  Point a_, b_;
+};
+class SpherocylinderSegment {
+ public:
+  SpherocylinderSegment(const Point& a, const Point& b, double r) : a_(a), b_(b), r_(r) {}
+  const Point& start() const { return a_; }
+  const Point& end() const { return b_; }
+  double radius() const { return r_; }
+
+ private:
+  Point a_, b_;
+  double r_;
+};
+
+// ---- batched entry points (device arrays, reference layouts) --------------------------------------------------------
+inline void compute_aabb_sphere_batch(mb200_stream st, int64_t n, const double* center, const double* radius, double* aabb) {
+  check(mb200_compute_aabb_sphere(st, n, center, radius, aabb), "mb200_compute_aabb_sphere");
+}
+inline void compute_aabb_spherocylinder_batch(mb200_stream st, int64_t n, const double* center, const double* quat,
+                                              const double* radius, const double* length, double* aabb) {
+  check(mb200_compute_aabb_spherocylinder(st, n, center, quat, radius, length, aabb), "mb200_compute_aabb_spherocylinder");
+}
+inline void compute_aabb_segment_batch(mb200_stream st, int64_t n, const double* start, const double* end,
+                                       const double* radius, double* aabb) {
+  check(mb200_compute_aabb_segment(st, n, start, end, radius, aabb), "mb200_compute_aabb_segment");
+}
+
+namespace detail {
+inline DeviceVector<double> up(std::initializer_list<double> v) { return DeviceVector<double>(std::vector<double>(v)); }
+inline DeviceVector<double> up3(const Vector3& p) { return up({p[0], p[1], p[2]}); }
+inline Vector3 down3(const DeviceVector<double>& d) {
+  const std::vector<double> h = d.to_host();
+  return {h[0], h[1], h[2]};
+}
+inline AABB down_aabb(const DeviceVector<double>& d) {
+  const std::vector<double> h = d.to_host();
+  return AABB({h[0], h[1], h[2]}, {h[3], h[4], h[5]});
+}
+}  // namespace detail
+
+// ---- the reference's single-object signatures ---------------------------------------------------------------------
+inline AABB compute_aabb(const Sphere& s) {
+  auto c = detail::up3(s.center()), r = detail::up({s.radius()});
+  DeviceVector<double> out(6);
+  compute_aabb_sphere_batch(nullptr, 1, c.data(), r.data(), out.data());
+  return detail::down_aabb(out);
+}
+inline AABB compute_aabb(const Spherocylinder& s) {
+  auto c = detail::up3(s.center()), r = detail::up({s.radius()}), len = detail::up({s.length()});
+  const Quaternion& o = s.orientation();
+  auto q = detail::up({o.q[0], o.q[1], o.q[2], o.q[3]});
+  DeviceVector<double> out(6);
+  compute_aabb_spherocylinder_batch(nullptr, 1, c.data(), q.data(), r.data(), len.data(), out.data());
+  return detail::down_aabb(out);
+}
+inline AABB compute_aabb(const SpherocylinderSegment& s) {
+  auto a = detail::up3(s.start()), b = detail::up3(s.end()), r = detail::up({s.radius()});
+  DeviceVector<double> out(6);
+  compute_aabb_segment_batch(nullptr, 1, a.data(), b.data(), r.data(), out.data());
+  return detail::down_aabb(out);
+}
+
+inline double distance(const Sphere& a, const Sphere& b, Vector3& sep) {
+  auto c1 = detail::up3(a.center()), c2 = detail::up3(b.center()), r1 = detail::up({a.radius()}), r2 = detail::up({b.radius()});
+  DeviceVector<double> d(1), s(3);
+  check(mb200_distance_sphere_sphere(nullptr, 1, c1.data(), r1.data(), c2.data(), r2.data(), d.data(), s.data()),
+        "mb200_distance_sphere_sphere");
+  sep = detail::down3(s);
+  return d.to_host()[0];
+}
+inline double distance(const Sphere& a, const Sphere& b) {
+  Vector3 sep;
+  return distance(a, b, sep);
+}
+inline double distance(SharedNormalSigned, const Sphere& a, const Sphere& b) { return distance(a, b); }
+inline double distance(SharedNormalSigned, const Sphere& a, const Sphere& b, Vector3& sep) { return distance(a, b, sep); }
+
+inline double distance(const LineSegment& l, const LineSegment& m, Point& cp1, Point& cp2, double& s, double& t,
+                       Vector3& sep) {
+  auto l0 = detail::up3(l.start()), l1 = detail::up3(l.end()), m0 = detail::up3(m.start()), m1 = detail::up3(m.end());
+  DeviceVector<double> d(1), ds(1), dt(1), c1(3), c2(3), sv(3);
+  check(mb200_distance_segment_segment(nullptr, 1, l0.data(), l1.data(), m0.data(), m1.data(), d.data(), ds.data(),
+                                       dt.data(), c1.data(), c2.data(), sv.data()),
+        "mb200_distance_segment_segment");
+  cp1 = detail::down3(c1), cp2 = detail::down3(c2), sep = detail::down3(sv);
+  s = ds.to_host()[0], t = dt.to_host()[0];
+  return d.to_host()[0];
+}
+inline double distance(const LineSegment& l, const LineSegment& m) {
+  Point a, b;
+  Vector3 sep;
+  double s, t;
+  return distance(l, m, a, b, s, t, sep);
+}
+inline double distance(SharedNormalSigned, const LineSegment& l, const LineSegment& m, Point& cp1, Point& cp2, double& s,
+                       double& t, Vector3& sep) {
+  return distance(l, m, cp1, cp2, s, t, sep);
+}
+
+inline double distance(const Point& x, const LineSegment& seg, Point& cp, double& t, Vector3& sep) {
+  auto px = detail::up3(x), p1 = detail::up3(seg.start()), p2 = detail::up3(seg.end());
+  DeviceVector<double> d(1), dt(1), c(3), sv(3);
+  check(mb200_distance_point_segment(nullptr, 1, px.data(), p1.data(), p2.data(), d.data(), dt.data(), c.data(), sv.data()),
+        "mb200_distance_point_segment");
+  cp = detail::down3(c), sep = detail::down3(sv), t = dt.to_host()[0];
+  return d.to_host()[0];
+}
+inline double distance(const LineSegment& seg, const Sphere& sph, Point& cp, double& t, Vector3& sep) {
+  auto p1 = detail::up3(seg.start()), p2 = detail::up3(seg.end()), c = detail::up3(sph.center()), r = detail::up({sph.radius()});
+  DeviceVector<double> d(1), dt(1), cpd(3), sv(3);
+  check(mb200_distance_segment_sphere(nullptr, 1, p1.data(), p2.data(), c.data(), r.data(), d.data(), dt.data(),
+                                      cpd.data(), sv.data()),
+        "mb200_distance_segment_sphere");
+  cp = detail::down3(cpd), sep = detail::down3(sv), t = dt.to_host()[0];
+  return d.to_host()[0];
+}
+
+}  // namespace geom
+}  // namespace mundy_b200
+#endif  // MUNDY_B200_GEOM_HPP_

@@ -72,6 +72,11 @@ SIGNATURES = {
     "mb200_kernel_launch_count": (c_i64, []),
     "mb200_profile_enable": (C.c_int, [C.c_int]),
     "mb200_profile_read": (C.c_int, [C.c_int, P(c_dbl), P(c_i64)]),
+    "mb200_device_alloc": (C.c_int, [P(vp), c_i64]),
+    "mb200_device_free": (C.c_int, [vp]),
+    "mb200_copy_to_device": (C.c_int, [vp, vp, vp, c_i64]),
+    "mb200_copy_to_host": (C.c_int, [vp, vp, vp, c_i64]),
+    "mb200_stream_synchronize": (C.c_int, [vp]),
     "mb200_compute_aabb_sphere": (C.c_int, [vp, c_i64, vp, vp, vp]),
     "mb200_compute_aabb_spherocylinder": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp]),
     "mb200_compute_aabb_segment": (C.c_int, [vp, c_i64, vp, vp, vp, vp]),

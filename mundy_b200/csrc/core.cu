@@ -104,6 +104,35 @@ int mb200_device_count(void) {
   return count;
 }
 
+int mb200_device_alloc(void** out, int64_t bytes) {
+  MB200_REQUIRE(out && bytes >= 0, "bad arguments");
+  MB200_TRY(mb200::require_device());
+  *out = nullptr;
+  if (bytes > 0) MB200_CUDA(cudaMalloc(out, static_cast<size_t>(bytes)));
+  return MB200_OK;
+}
+int mb200_device_free(void* ptr) {
+  if (ptr) MB200_CUDA(cudaFree(ptr));
+  return MB200_OK;
+}
+int mb200_copy_to_device(mb200_stream stream, void* dst, const void* src_h, int64_t bytes) {
+  MB200_REQUIRE(bytes >= 0 && (bytes == 0 || (dst && src_h)), "bad arguments");
+  MB200_TRY(mb200::require_device());
+  if (bytes > 0) MB200_CUDA(cudaMemcpyAsync(dst, src_h, static_cast<size_t>(bytes), cudaMemcpyHostToDevice, mb200::as_stream(stream)));
+  return MB200_OK;
+}
+int mb200_copy_to_host(mb200_stream stream, void* dst_h, const void* src, int64_t bytes) {
+  MB200_REQUIRE(bytes >= 0 && (bytes == 0 || (dst_h && src)), "bad arguments");
+  MB200_TRY(mb200::require_device());
+  if (bytes > 0) MB200_CUDA(cudaMemcpyAsync(dst_h, src, static_cast<size_t>(bytes), cudaMemcpyDeviceToHost, mb200::as_stream(stream)));
+  return MB200_OK;
+}
+int mb200_stream_synchronize(mb200_stream stream) {
+  MB200_TRY(mb200::require_device());
+  MB200_CUDA(cudaStreamSynchronize(mb200::as_stream(stream)));
+  return MB200_OK;
+}
+
 int64_t mb200_kernel_launch_count(void) { return mb200::g_launches.load(std::memory_order_relaxed); }
 
 int mb200_profile_enable(int on) {
