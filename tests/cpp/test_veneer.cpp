@@ -104,9 +104,13 @@ int main() {
     auto [r0, x0] = run(make_b200_cqpp(nullptr, Aop, dq, convex::Unconstrained{}), make_pgd_solution_strategy(be, cfg));
     EXPECT_TRUE(r0.converged);
     for (int i = 0; i < 3; ++i) EXPECT_NEAR(x0[i], xs[i], 1e-5);
-    auto [r1, x1] = run(make_b200_cqpp(nullptr, Aop, dq, convex::Box{0.0, 2.5}),
-                        make_pgd_solution_strategy(be, convex::BBStepStrategy{}, convex::LinfNormProjectedGradientResidual{}, cfg));
+    auto [r1, x1] = run(make_b200_cqpp(nullptr, Aop, dq, convex::Box{0.0, 2.5}), make_pgd_solution_strategy(be, cfg));
     EXPECT_TRUE(r1.converged && x1[2] == 2.5 && x1[0] <= 2.5 && x1[1] <= 2.5);
+    // the projected-gradient residual policy (:434-466) is written for the bound x >= 0
+    auto [r2, x2] = run(make_b200_cqpp(nullptr, Aop, dq, convex::LowerBound{0.0}),
+                        make_pgd_solution_strategy(be, convex::BBStepStrategy{}, convex::LinfNormProjectedGradientResidual{}, cfg));
+    EXPECT_TRUE(r2.converged);
+    for (int i = 0; i < 3; ++i) EXPECT_NEAR(x2[i], xs[i], 1e-5);
     // LCP through solve_lcp: w = A x + q >= 0, x >= 0, x.w = 0; the unconstrained optimum is positive => same solution
     {
       DeviceVector<double> x(std::vector<double>(3, 99.99)), g(3), xt(3), gt(3);
