@@ -292,6 +292,39 @@ int mb200_collision_step_host(mb200_neighbor_links* links, mb200_stream stream, 
                               double* F_col_h, double* T_col_h, double* U_out_h, double* W_out_h,
                               mb200_step_stats* stats_h);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Multi-GPU (one process per GPU, NCCL over NVLink / NVSwitch). Replaces the MPI usage of the STK drivers on this path
+ * (scrap/lcp_spheres/NGPSpheresLCP.cpp:371,450-452 all_reduce of the residual and the BB sums; :256-283 ghosting).
+ *
+ * Decomposition: the caller orders the global body arrays along a space-filling curve (mundy_b200/dist.py: Hilbert
+ * index of the centre) and every rank holds a replica of them; rank r OWNS the contiguous index block
+ * [r n/W, (r+1) n/W). A rank works on its owned bodies plus the foreign bodies within search reach (ghosts). A link
+ * with one owned end is kept by both owners and its gamma is computed redundantly (bit-identically) on both; it is
+ * counted in the global sums by the owner of its lower-index body (scrap/UnitTestMundy.cpp:553-555). Per solver
+ * iteration the owners' velocity records go to the ghost rows (NCCL send/recv) and the four scalars are all-gathered;
+ * per step the advanced owned state is all-gathered into every replica.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct mb200_comm mb200_comm;
+#define MB200_COMM_ID_BYTES 128
+/* Rank 0 creates the id (host buffer of MB200_COMM_ID_BYTES) and hands it to the other ranks by any means. */
+int mb200_comm_get_unique_id(char* id_out_h);
+/* Collective over all ranks. The calling thread's current CUDA device is the rank's GPU. */
+int mb200_comm_create(mb200_comm** out, int world, int rank, const char* id_h);
+int mb200_comm_destroy(mb200_comm* comm);
+int mb200_comm_world(const mb200_comm* comm);
+int mb200_comm_rank(const mb200_comm* comm);
+
+/* One collision timestep on the replicated global body set (device arrays of ALL n bodies on every rank; n must be a
+ * multiple of the world size). On return every replica holds the advanced centres / quaternions of all bodies.
+ * F_ext / T_ext: replicated [3n] or NULL. F_col / U_out: optional [3n]; only the owned block is written.
+ * stats_h: links and launches of THIS rank; lcp fields are global. Collective; synchronises the stream. */
+int mb200_collision_step_dist(mb200_neighbor_links* links, mb200_comm* comm, mb200_stream stream,
+                              const mb200_bodies* global_bodies, const mb200_step_params* params,
+                              const double* F_ext, const double* T_ext, double* F_col, double* U_out,
+                              mb200_step_stats* stats_h);
+/* Bodies (owned + ghosts) and ghosts alone in the last distributed build of this rank. */
+int mb200_dist_local_counts(const mb200_neighbor_links* links, int64_t* n_local_h, int64_t* n_ghost_rows_h);
+
 /* Total kernels launched by this library in the calling process (a monotone counter; for bench accounting). */
 int64_t mb200_kernel_launch_count(void);
 
@@ -311,7 +344,9 @@ enum mb200_stage {
   MB200_STAGE_LCP_BODY = 5,   /* BBPGD: gamma update, F = D gamma, U = M F           one region per launch */
   MB200_STAGE_LCP_RATE = 6,   /* BBPGD: gamma update, g = D^T U, residual, BB dots   one region per launch */
   MB200_STAGE_EULER = 7,      /* velocity totals, Euler update, scatter to the caller's order            */
-  MB200_STAGE_COUNT = 8
+  MB200_STAGE_LCP_COMM = 8,   /* multi-GPU: velocity halo (pack, NCCL send/recv, unpack), all-gather of the sums */
+  MB200_STAGE_STATE_COMM = 9, /* multi-GPU: all-gather of the advanced body state, rebuild-flag all-reduce       */
+  MB200_STAGE_COUNT = 10
 };
 int mb200_profile_enable(int on);
 int mb200_profile_read(int stage, double* ms_total_h, int64_t* regions_h);

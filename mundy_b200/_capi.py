@@ -110,6 +110,13 @@ SIGNATURES = {
     "mb200_euler_update": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, c_dbl]),
     "mb200_abc_flow_force": (C.c_int, [vp, c_i64, vp, vp]),
     "mb200_collision_step": (C.c_int, [vp, vp, P(Bodies), P(StepParams), vp, vp, vp, vp, vp, vp, P(StepStats)]),
+    "mb200_comm_get_unique_id": (C.c_int, [vp]),
+    "mb200_comm_create": (C.c_int, [P(vp), C.c_int, C.c_int, vp]),
+    "mb200_comm_destroy": (C.c_int, [vp]),
+    "mb200_comm_world": (C.c_int, [vp]),
+    "mb200_comm_rank": (C.c_int, [vp]),
+    "mb200_collision_step_dist": (C.c_int, [vp, vp, vp, P(Bodies), P(StepParams), vp, vp, vp, vp, P(StepStats)]),
+    "mb200_dist_local_counts": (C.c_int, [vp, P(c_i64), P(c_i64)]),
     "mb200_collision_step_host": (C.c_int, [vp, vp, P(Bodies), P(StepParams), vp, vp, vp, vp, vp, vp, P(StepStats)]),
 }
 

@@ -123,7 +123,8 @@ __global__ void __launch_bounds__(256)
     find_pairs_kernel(int64_t n, const D4* __restrict__ sr, const D4* __restrict__ b0, const D4* __restrict__ b1,
                       const uint32_t* __restrict__ perm, const int2* __restrict__ cell_range, GridParams gp,
                       double cutoff, uint32_t* __restrict__ counts, const int64_t* __restrict__ rowptr,
-                      int2* __restrict__ pairs, int32_t* __restrict__ slots, int slot_cap) {
+                      int2* __restrict__ pairs, int32_t* __restrict__ slots, int slot_cap,
+                      const uint8_t* __restrict__ own) {
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
   const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
@@ -139,6 +140,8 @@ __global__ void __launch_bounds__(256)
     }
   }
   const D4 si = ldg256(sr + i);
+  // multi-GPU: links between two ghost bodies belong to other ranks
+  const bool own_i = own ? own[i] != 0 : true;
   D4 b0i{0, 0, 0, 0}, b1i{0, 0, 0, 0};
   uint32_t pi = 0;
   if (FILTER) {
@@ -240,8 +243,8 @@ __global__ void __launch_bounds__(256)
     D4 sa{0, 0, 0, 0}, sb{0, 0, 0, 0};
     if (ja >= 0) sa = ldg256(sr + ja);
     if (jb >= 0) sb = ldg256(sr + jb);
-    const bool ka = (ja >= 0) && is_candidate(si, sa);
-    const bool kb = (jb >= 0) && is_candidate(si, sb);
+    const bool ka = (ja >= 0) && is_candidate(si, sa) && (own_i || own[ja]);
+    const bool kb = (jb >= 0) && is_candidate(si, sb) && (own_i || own[jb]);
     if (FILTER) {
       const uint32_t ma = __ballot_sync(0xffffffffu, ka), mb = __ballot_sync(0xffffffffu, kb);
       if (ka) q[qn + __popc(ma & lt_mask)] = ja;
@@ -311,7 +314,14 @@ int bits_for(int64_t n) {
 
 }  // namespace
 
-int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, const double* explicit_S) {
+__global__ void __launch_bounds__(256) gather_u8_kernel(int64_t n, const uint32_t* __restrict__ perm,
+                                                        const uint8_t* __restrict__ src, uint8_t* __restrict__ dst) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k < n) dst[k] = src[perm[k]];
+}
+
+int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, const double* explicit_S,
+                const uint8_t* owned) {
   const int64_t n = b->n;
   h->n = n;
   h->npairs = 0;
@@ -377,6 +387,12 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   MB200_TRY(radix_sort_u32(st, n, keys.p, keys_alt.p, h->perm.p, vals_alt.p, key_bits));
   gather_records_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, sr.p, sr_s.p);
   MB200_LAUNCHED();
+  Scratch<uint8_t> own_s;  // ownership flags in Morton order (multi-GPU only)
+  if (owned) {
+    MB200_TRY(own_s.alloc(n, st));
+    gather_u8_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, owned, own_s.p);
+    MB200_LAUNCHED();
+  }
   if (filter) {
     MB200_TRY(b0s.alloc(n, st));
     MB200_TRY(b1s.alloc(n, st));
@@ -405,10 +421,10 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   const int pgrid = grid_for(n * 32, 256);
   if (filter)
     find_pairs_kernel<false, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
-                                                         counts.p, nullptr, nullptr, slots.p, slot_cap);
+                                                         counts.p, nullptr, nullptr, slots.p, slot_cap, own_s.p);
   else
     find_pairs_kernel<false, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
-                                                          cutoff, counts.p, nullptr, nullptr, slots.p, slot_cap);
+                                                          cutoff, counts.p, nullptr, nullptr, slots.p, slot_cap, own_s.p);
   MB200_LAUNCHED();
   MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, rowptr.p));
   int64_t total = 0;
@@ -424,14 +440,26 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
     int2* out = reinterpret_cast<int2*>(h->pairs.p);
     if (filter)
       find_pairs_kernel<true, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
-                                                          nullptr, rowptr.p, out, slots.p, slot_cap);
+                                                          nullptr, rowptr.p, out, slots.p, slot_cap, own_s.p);
     else
       find_pairs_kernel<true, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
-                                                           cutoff, nullptr, rowptr.p, out, slots.p, slot_cap);
+                                                           cutoff, nullptr, rowptr.p, out, slots.p, slot_cap, own_s.p);
     MB200_LAUNCHED();
   }
   // 5. body-major incidence lists for the contact operator
   return build_incidence(st, n, total, h->pairs.p, &h->inc);
+}
+
+// Device flag (h->flag) = 1 when some body moved more than half the buffer since the last build. No host sync.
+int links_moved_flag(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b) {
+  MB200_TRY(h->flag.reserve(1));
+  MB200_CUDA(cudaMemsetAsync(h->flag.p, 0, sizeof(int32_t), st));
+  if (b->n == 0) return MB200_OK;
+  const bool shape = h->filter == MB200_FILTER_SHAPE_DISTANCE && h->rods;
+  moved_kernel<<<grid_for(b->n, 256), 256, 0, st>>>(b->n, b->center, h->ref_center.p, b->quat, b->length, b->kind,
+                                                   shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p);
+  MB200_LAUNCHED();
+  return MB200_OK;
 }
 
 int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, int force, int* rebuilt_h) {
@@ -451,7 +479,7 @@ int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies*
   }
   if (rebuild) {
     StageScope ps(MB200_STAGE_BROADPHASE, st);
-    MB200_TRY(build_links(st, h, b, nullptr));
+    MB200_TRY(build_links(st, h, b, nullptr, nullptr));
   }
   if (rebuilt_h) *rebuilt_h = rebuild ? 1 : 0;
   return MB200_OK;

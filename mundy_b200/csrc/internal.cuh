@@ -2,6 +2,8 @@
 #pragma once
 #include "common.cuh"
 
+struct mb200_comm;
+
 namespace mb200 {
 
 // narrow_phase.cu ------------------------------------------------------------------------------------------------
@@ -31,12 +33,30 @@ struct RecordSystem {
   const int32_t* kind;
   double mu, dt;
 };
+// Multi-GPU hooks of the solver (null => one GPU). Body indices are the solver's (the order the records index).
+struct DistSolve {
+  mb200_comm* comm;
+  const uint8_t* counted;      // [npairs] 1 = this rank adds the contact to the global residual / BB sums
+  int npeers;
+  int peer[16];                // ranks exchanged with
+  int64_t send_off[17];        // prefix offsets (in bodies) into send_idx, per peer
+  int64_t recv_off[17];
+  const uint32_t* send_idx;    // owned bodies whose velocity records go to a peer
+  const uint32_t* recv_idx;    // ghost rows filled from a peer (same order as the peer's send list)
+  D4* sendbuf;                 // 2 records per body capacity
+  D4* recvbuf;
+  double* red;                 // device scratch: [4] local totals followed by [4 * world] gathered
+};
 int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& inc, const mb200_lcp_params* params,
                     const double* U_ext, const double* W_ext, const double* gamma0, double* gamma_out,
-                    double* phi0_out, double* F, double* T, double* U, double* W, mb200_collision_result* result_h);
+                    double* phi0_out, double* F, double* T, double* U, double* W, mb200_collision_result* result_h,
+                    const DistSolve* dist);
 // Narrow phase straight into contact records (the step's path).
-int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const D4* b0, const D4* b1, bool six,
-                            D4* rec);
+// perm (Morton -> caller index, nullable): pairs are evaluated with the lower caller index first.
+int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const uint32_t* perm, const D4* b0,
+                            const D4* b1, bool six, D4* rec);
+// step.cu: the step after the link list is known (dist != NULL on the multi-GPU path)
+
 
 // The BBPGD solve on caller-layout arrays and an already-built incidence structure (used by mb200_resolve_collisions and the step).
 int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const Incidence& inc,

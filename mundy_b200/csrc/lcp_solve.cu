@@ -20,6 +20,7 @@
 //               the last CTA to finish reduces the per-CTA partials in index order and advances alpha / done.
 // Every kernel returns at once when `done` is set, so the host enqueues iterations in batches and reads the 48-byte
 // solver state back between batches only.
+#include "comm.cuh"
 #include "internal.cuh"
 #include "lcp.cuh"
 
@@ -49,6 +50,9 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
   int32_t it_cap;  // max iterations (or the fixed count)
   LcpState* state;
   double* partials;  // [4 * rate grid]
+  // multi-GPU (null on one GPU): contacts this rank adds to the global sums; where the last CTA leaves the local totals
+  const uint8_t* counted;
+  double* red_local;
 };
 
 __device__ inline double2 ldg128(const double2* p) {
@@ -323,6 +327,63 @@ __global__ void __launch_bounds__(kBodyThreads)
 
 constexpr int kRateThreads = 256;
 
+// End of an operator application: residual test, next BB step length, iteration cap (KokkosLCP.cpp:735-750, 785-848).
+__device__ inline void advance_state(LcpState* s, double res, double xx, double xg, double gg, int it, int mode,
+                                     int fixed, double tol, int it_cap) {
+  s->res = res;
+  s->it = it;
+  if (!fixed && res < tol) {  // strict <, KokkosLCP.cpp:744,788
+    s->done = 1;
+    s->converged = 1;
+    return;
+  }
+  if (mode == 0) {
+    s->alpha = 1.0 / res;  // :750
+  } else {
+    double num, den;  // :831-848; `it` was already incremented at the loop top, so iteration 1 takes BB2
+    if (it % 2 == 0) {
+      num = xx, den = xg;
+    } else {
+      num = xg, den = gg;
+    }
+    if (fabs(den) < 1e-12) den += 1e-12;
+    s->alpha = num / den;
+  }
+  if (it >= it_cap) s->done = 1;
+}
+
+// Multi-GPU: the ranks' totals {res, xx, xg, gg} gathered in rank order -> the same state on every rank.
+__global__ void advance_kernel(LcpState* s, const double* __restrict__ red_all, int world, int it, int mode, int fixed,
+                               double tol, int it_cap) {
+  if (threadIdx.x != 0 || s->done) return;
+  double res = -1.0, xx = 0.0, xg = 0.0, gg = 0.0;
+  for (int r = 0; r < world; ++r) {
+    res = fmax(res, red_all[4 * r]);
+    xx += red_all[4 * r + 1], xg += red_all[4 * r + 2], gg += red_all[4 * r + 3];
+  }
+  advance_state(s, res, xx, xg, gg, it, mode, fixed, tol, it_cap);
+}
+
+// Halo of the body velocity records: owners' records -> send buffer, received records -> ghost rows.
+__global__ void __launch_bounds__(256) halo_pack_kernel(int64_t count, int recs, const uint32_t* __restrict__ idx,
+                                                        const D4* __restrict__ vel, D4* __restrict__ buf,
+                                                        const LcpState* __restrict__ state) {
+  if (state->done) return;
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= count * recs) return;
+  const int64_t b = idx[k / recs];
+  buf[k] = vel[b * recs + (k % recs)];
+}
+__global__ void __launch_bounds__(256) halo_unpack_kernel(int64_t count, int recs, const uint32_t* __restrict__ idx,
+                                                          const D4* __restrict__ buf, D4* __restrict__ vel,
+                                                          const LcpState* __restrict__ state) {
+  if (state->done) return;
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= count * recs) return;
+  const int64_t b = idx[k / recs];
+  vel[b * recs + (k % recs)] = buf[k];
+}
+
 // MODE 0: initial pass (state holds gamma_0; g_0 = D^T M D gamma_0, residual only). MODE 1: iteration pass.
 template <bool SIX, int MODE>
 __global__ void __launch_bounds__(kRateThreads)
@@ -355,6 +416,7 @@ __global__ void __launch_bounds__(kRateThreads)
     const double gam = gamma_of<MODE>(sp, r0.w, alpha, a.dt, first);
     const double g = contact_rate<SIX>(n, ui, uj, wi, wj, ai, aj);
     st_cur[c] = make_double2(gam, g);
+    if (a.counted && !a.counted[c]) continue;  // a cut contact is summed by the rank that owns its first body
     const double sep_new = r0.w + a.dt * g;  // KokkosLCP.cpp:500-521
     const double v = (gam < 1e-12) ? fabs(fmin(sep_new, 0.0)) : fabs(sep_new);
     res = fmax(res, v);
@@ -398,25 +460,10 @@ __global__ void __launch_bounds__(kRateThreads)
   if (t == 0) {
     LcpState* s = a.state;
     s->ticket = 0;
-    s->res = res;
-    s->it = it;
-    if (!a.fixed && res < a.tol) {  // strict <, KokkosLCP.cpp:744,788
-      s->done = 1;
-      s->converged = 1;
+    if (a.red_local) {  // multi-GPU: the totals go through an all-gather, advance_kernel finishes the iteration
+      a.red_local[0] = res, a.red_local[1] = xx, a.red_local[2] = xg, a.red_local[3] = gg;
     } else {
-      if (MODE == 0) {
-        s->alpha = 1.0 / res;  // :750
-      } else {
-        double num, den;  // :831-848; `it` was already incremented at the loop top, so iteration 1 takes BB2
-        if (it % 2 == 0) {
-          num = xx, den = xg;
-        } else {
-          num = xg, den = gg;
-        }
-        if (fabs(den) < 1e-12) den += 1e-12;
-        s->alpha = num / den;
-      }
-      if (it >= a.it_cap) s->done = 1;
+      advance_state(s, res, xx, xg, gg, it, MODE, a.fixed, a.tol, a.it_cap);
     }
   }
 }
@@ -439,7 +486,8 @@ int resident_grid(K kernel, int threads) {
 
 int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& inc, const mb200_lcp_params* params,
                     const double* U_ext, const double* W_ext, const double* gamma0, double* gamma_out,
-                    double* phi0_out, double* F, double* T, double* U, double* W, mb200_collision_result* result_h) {
+                    double* phi0_out, double* F, double* T, double* U, double* W, mb200_collision_result* result_h,
+                    const DistSolve* dist) {
   const int64_t n = sys.n, C = sys.npairs;
   const bool six = sys.six;
   const bool fixed = params->fixed_iters >= 0;
@@ -448,7 +496,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   static thread_local PinnedState pinned;
   if (!pinned.h) MB200_CUDA(cudaMallocHost(reinterpret_cast<void**>(&pinned.h), sizeof(LcpState)));
 
-  if (C == 0) {  // nothing to solve: zero force / velocity, residual identity of the max-reduction (-1)
+  if (C == 0 && !dist) {  // nothing to solve: zero force / velocity, residual identity of the max-reduction (-1)
     if (F) MB200_CUDA(cudaMemsetAsync(F, 0, 3 * n * sizeof(double), st));
     if (six && T) MB200_CUDA(cudaMemsetAsync(T, 0, 3 * n * sizeof(double), st));
     if (U) MB200_CUDA(cudaMemsetAsync(U, 0, 3 * n * sizeof(double), st));
@@ -486,6 +534,46 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   a.mu = sys.mu, a.dt = sys.dt, a.tol = params->tol;
   a.fixed = fixed ? 1 : 0, a.it_cap = it_cap;
   a.state = state.p, a.partials = partials.p;
+  a.counted = dist ? dist->counted : nullptr;
+  a.red_local = dist ? dist->red : nullptr;
+  const NcclApi* nccl = dist ? nccl_api() : nullptr;
+  if (dist && !nccl) return MB200_ERR_COMM;
+  const int recs = six ? 2 : 1;
+  // multi-GPU: ghost rows of the velocity records come from their owners after every body pass
+  auto halo = [&]() -> int {
+    if (!dist) return MB200_OK;
+    StageScope ps(MB200_STAGE_LCP_COMM, st);
+    const int64_t ns = dist->send_off[dist->npeers], nr = dist->recv_off[dist->npeers];
+    if (ns > 0) {
+      halo_pack_kernel<<<grid_for(ns * recs, 256), 256, 0, st>>>(ns, recs, dist->send_idx, vel.p, dist->sendbuf, state.p);
+      MB200_LAUNCHED();
+    }
+    MB200_NCCL(nccl->GroupStart());
+    for (int k = 0; k < dist->npeers; ++k) {
+      const int64_t cs = dist->send_off[k + 1] - dist->send_off[k], cr = dist->recv_off[k + 1] - dist->recv_off[k];
+      if (cs > 0)
+        MB200_NCCL(nccl->Send(dist->sendbuf + dist->send_off[k] * recs, static_cast<size_t>(cs) * recs * 4, ncclDouble,
+                              dist->peer[k], dist->comm->comm, st));
+      if (cr > 0)
+        MB200_NCCL(nccl->Recv(dist->recvbuf + dist->recv_off[k] * recs, static_cast<size_t>(cr) * recs * 4, ncclDouble,
+                              dist->peer[k], dist->comm->comm, st));
+    }
+    MB200_NCCL(nccl->GroupEnd());
+    if (nr > 0) {
+      halo_unpack_kernel<<<grid_for(nr * recs, 256), 256, 0, st>>>(nr, recs, dist->recv_idx, dist->recvbuf, vel.p, state.p);
+      MB200_LAUNCHED();
+    }
+    return MB200_OK;
+  };
+  // multi-GPU: all-gather of the ranks' totals (rank order => identical sums everywhere), then the state update
+  auto reduce = [&](int it_now, int mode) -> int {
+    if (!dist) return MB200_OK;
+    StageScope ps(MB200_STAGE_LCP_COMM, st);
+    MB200_NCCL(nccl->AllGather(dist->red, dist->red + 4, 4, ncclDouble, dist->comm->comm, st));
+    advance_kernel<<<1, 32, 0, st>>>(state.p, dist->red + 4, dist->comm->world, it_now, mode, a.fixed, a.tol, a.it_cap);
+    MB200_LAUNCHED();
+    return MB200_OK;
+  };
 
   {
     StageScope ps(MB200_STAGE_LCP_SETUP, st);
@@ -511,6 +599,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
       body_pass_kernel<false, 0, false><<<body_grid, kBodyThreads, 0, st>>>(a, 0, s0.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
     MB200_LAUNCHED();
   }
+  MB200_TRY(halo());
   {
     StageScope ps(MB200_STAGE_LCP_RATE, st);
     if (six)
@@ -519,6 +608,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
       rate_pass_kernel<false, 0><<<rate_grid, kRateThreads, 0, st>>>(a, 0, 0, s0.p, s1.p);
     MB200_LAUNCHED();
   }
+  MB200_TRY(reduce(0, 0));
 
   // iteration `it` reads the previous state from s1 when it is odd (s0 when even) and writes the other buffer
   int it = 0;
@@ -544,6 +634,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
           body_pass_kernel<false, 1, false><<<body_grid, kBodyThreads, 0, st>>>(a, first, prev, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
         MB200_LAUNCHED();
       }
+      MB200_TRY(halo());
       {
         StageScope ps(MB200_STAGE_LCP_RATE, st);
         if (six)
@@ -552,6 +643,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
           rate_pass_kernel<false, 1><<<rate_grid, kRateThreads, 0, st>>>(a, it, first, prev, cur);
         MB200_LAUNCHED();
       }
+      MB200_TRY(reduce(it, 1));
     }
     if (batch < 32) batch *= 2;
   }
@@ -604,7 +696,8 @@ int resolve_collisions_impl(cudaStream_t st, const mb200_contact_op* op, const I
     MB200_LAUNCHED();
   }
   RecordSystem sys{op->n, C, six, pairs, rec.p, op->quat, op->radius, op->kind, op->viscosity, op->dt};
-  return resolve_records(st, sys, inc, params, U_ext, W_ext, gamma, gamma, U_ext ? phi0 : nullptr, F, T, U, W, result_h);
+  return resolve_records(st, sys, inc, params, U_ext, W_ext, gamma, gamma, U_ext ? phi0 : nullptr, F, T, U, W, result_h,
+                         nullptr);
 }
 
 }  // namespace mb200

@@ -25,11 +25,37 @@ struct mb200_neighbor_links {
   // device mirrors of the host arrays of mb200_collision_step_host
   mb200::DevBuf<double> hm_center, hm_quat, hm_radius, hm_length, hm_fext, hm_text, hm_fcol, hm_tcol, hm_u, hm_w;
   mb200::DevBuf<int32_t> hm_kind;
+
+  // ---- multi-GPU state (dist_step.cu) ----
+  struct Dist {
+    bool built = false;
+    int64_t n_global = 0, n_local = 0, n_own = 0, o_beg = 0;
+    mb200::DevBuf<uint32_t> gidx;      // local -> global body index                  [n_local]
+    mb200::DevBuf<uint8_t> owned;      // local body owned by this rank                [n_local]
+    mb200::DevBuf<double> center, quat, radius, length, fext, text, fcol, uout;   // local body arrays
+    mb200::DevBuf<int32_t> kind;
+    mb200::DevBuf<uint8_t> counted;    // contact counted by this rank                 [npairs]
+    mb200::DevBuf<uint32_t> inv_perm;  // local caller index -> Morton index           [n_local]
+    mb200::DevBuf<uint32_t> send_idx, recv_idx;
+    mb200::DevBuf<mb200::D4> sendbuf, recvbuf;
+    mb200::DevBuf<double> red;
+    mb200::DevBuf<int32_t> flag_all;
+    int npeers = 0;
+    int peer[16];
+    int64_t send_off[17], recv_off[17];
+  } dist;
 };
 
 namespace mb200 {
 // broadphase.cu: (re)build the link list from the bodies (explicit_S != NULL: search radii given, no buffer/filter).
-int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, const double* explicit_S);
+// owned != NULL (multi-GPU): per-body ownership flags in the caller's order; links between two non-owned bodies are dropped.
+int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, const double* explicit_S,
+                const uint8_t* owned);
+int links_moved_flag(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b);
+// step.cu
+int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodies, const mb200_step_params* params,
+              const double* F_ext, const double* T_ext, double* F_col, double* T_col, double* U_out, double* W_out,
+              int rebuilt, long long launches0, const DistSolve* dist, mb200_step_stats* stats_h);
 // pairs in the caller's indices, sorted by (i,j) with i<j, written to out[2*npairs]
 int canonical_pairs(cudaStream_t st, mb200_neighbor_links* h, int32_t* out);
 int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, int force, int* rebuilt_h);

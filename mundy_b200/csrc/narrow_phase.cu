@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(kTile)
 // Same arithmetic, written as solver contact records (lcp_solve.cu): R0 = {n, phi0}, R1 = {arm_i, (i,j)}, R2 = {arm_j, 0}.
 template <bool RODS, bool SIX>
 __global__ void __launch_bounds__(256)
-    narrow_phase_rec_kernel(int64_t npairs, const int2* __restrict__ pairs, const D4* __restrict__ b0,
-                            const D4* __restrict__ b1, D4* __restrict__ rec) {
+    narrow_phase_rec_kernel(int64_t npairs, const int2* __restrict__ pairs, const uint32_t* __restrict__ perm,
+                            const D4* __restrict__ b0, const D4* __restrict__ b1, D4* __restrict__ rec) {
   const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (c >= npairs) return;
   const int2 p = __ldg(pairs + c);
@@ -93,7 +93,18 @@ __global__ void __launch_bounds__(256)
     b1i = ldg256(b1 + p.x);
     b1j = ldg256(b1 + p.y);
   }
-  const PairGeom g = pair_geometry<RODS>(b0i, b1i, b0j, b1j);
+  // The pair is evaluated with the body of lower CALLER index first (the reference's (i<j) order, as the oracle does),
+  // whatever the Morton order of the two: results do not depend on the internal ordering or on the rank.
+  PairGeom g;
+  if (!perm || perm[p.x] < perm[p.y]) {
+    g = pair_geometry<RODS>(b0i, b1i, b0j, b1j);
+  } else {
+    const PairGeom r = pair_geometry<RODS>(b0j, b1j, b0i, b1i);
+    g.sep = r.sep;
+    g.n = V3{-r.n.x, -r.n.y, -r.n.z};
+    g.arm_i = r.arm_j;
+    g.arm_j = r.arm_i;
+  }
   if (SIX) {
     const long long bits = (static_cast<long long>(p.y) << 32) | static_cast<long long>(static_cast<uint32_t>(p.x));
     st256(rec + 3 * c, D4{g.n.x, g.n.y, g.n.z, g.sep});
@@ -106,15 +117,15 @@ __global__ void __launch_bounds__(256)
 
 }  // namespace
 
-int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const D4* b0, const D4* b1, bool six,
-                            D4* rec) {
+int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const uint32_t* perm, const D4* b0,
+                            const D4* b1, bool six, D4* rec) {
   if (npairs == 0) return MB200_OK;
   const int grid = grid_for(npairs, 256);
   const int2* p2 = reinterpret_cast<const int2*>(pairs);
   if (b1 && six)
-    narrow_phase_rec_kernel<true, true><<<grid, 256, 0, st>>>(npairs, p2, b0, b1, rec);
+    narrow_phase_rec_kernel<true, true><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, b1, rec);
   else if (!b1 && !six)
-    narrow_phase_rec_kernel<false, false><<<grid, 256, 0, st>>>(npairs, p2, b0, nullptr, rec);
+    narrow_phase_rec_kernel<false, false><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, nullptr, rec);
   else {
     set_error("narrow_phase_to_records: rods and 6-DOF records go together");
     return MB200_ERR_INVALID_ARGUMENT;

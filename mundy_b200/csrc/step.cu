@@ -149,7 +149,7 @@ int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, con
   cudaStream_t st = as_stream(stream);
   mb200_neighbor_links tmp;
   mb200_bodies b{n, const_cast<double*>(center), nullptr, search_radius, nullptr, nullptr};
-  MB200_TRY(build_links(st, &tmp, &b, search_radius));
+  MB200_TRY(build_links(st, &tmp, &b, search_radius, nullptr));
   *count_h = tmp.npairs;
   if (tmp.npairs > capacity) {
     set_error("pairs_out too small");
@@ -165,18 +165,13 @@ int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, con
 
 }  // extern "C"
 
-extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream, const mb200_bodies* bodies,
-                                    const mb200_step_params* params, const double* F_ext, const double* T_ext,
-                                    double* F_col, double* T_col, double* U_out, double* W_out,
-                                    mb200_step_stats* stats_h) {
-  MB200_REQUIRE(h && params, "null handle/params");
-  MB200_TRY(check_bodies(bodies));
-  MB200_TRY(require_device());
-  cudaStream_t st = as_stream(stream);
-  const long long launches0 = g_launches.load();
+namespace mb200 {
+
+// The step after the link list is known: records, narrow phase, BBPGD, Euler. `dist` != NULL on the multi-GPU path.
+int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodies, const mb200_step_params* params,
+              const double* F_ext, const double* T_ext, double* F_col, double* T_col, double* U_out, double* W_out,
+              int rebuilt, long long launches0, const DistSolve* dist, mb200_step_stats* stats_h) {
   const int64_t n = bodies->n;
-  int rebuilt = 0;
-  MB200_TRY(links_generate(st, h, bodies, params->force_rebuild, &rebuilt));
   const int64_t C = h->npairs;
   const bool rods = bodies->kind != nullptr;
   mb200_collision_result res{-1.0, 0, 1, 0.0};
@@ -211,7 +206,7 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
     }
     {  // narrow phase on the links
       StageScope ps(MB200_STAGE_NARROW, st);
-      MB200_TRY(narrow_phase_to_records(st, C, h->pairs.p, h->b0.p, rods ? h->b1.p : nullptr, rods, h->rec.p));
+      MB200_TRY(narrow_phase_to_records(st, C, h->pairs.p, h->perm.p, h->b0.p, rods ? h->b1.p : nullptr, rods, h->rec.p));
     }
     // LCP
     MB200_TRY(h->vec_c.reserve(3 * n));
@@ -227,7 +222,7 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
     double* U_s = h->vec_d.p;
     double* T_s = rods ? h->vec_e.p : nullptr;
     double* W_s = rods ? h->vec_f.p : nullptr;
-    MB200_TRY(resolve_records(st, sys, h->inc, &lp, Uext_s, Wext_s, nullptr, nullptr, nullptr, F_s, T_s, U_s, W_s, &res));
+    MB200_TRY(resolve_records(st, sys, h->inc, &lp, Uext_s, Wext_s, nullptr, nullptr, nullptr, F_s, T_s, U_s, W_s, &res, dist));
     if (params->throw_on_max_iters && params->fixed_iters < 0 && res.ite_count == params->max_iters && !res.converged) {
       set_error("Collision resolution did not converge!");  // scrap/lcp_spheres/NGPSpheresLCP.cpp:745-747
       if (stats_h) *stats_h = mb200_step_stats{res, C, rebuilt, static_cast<int32_t>(g_launches.load() - launches0)};
@@ -244,6 +239,23 @@ extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream
   MB200_CUDA(cudaStreamSynchronize(st));
   if (stats_h) *stats_h = mb200_step_stats{res, C, rebuilt, static_cast<int32_t>(g_launches.load() - launches0)};
   return MB200_OK;
+}
+
+
+}  // namespace mb200
+
+extern "C" int mb200_collision_step(mb200_neighbor_links* h, mb200_stream stream, const mb200_bodies* bodies,
+                                    const mb200_step_params* params, const double* F_ext, const double* T_ext,
+                                    double* F_col, double* T_col, double* U_out, double* W_out,
+                                    mb200_step_stats* stats_h) {
+  MB200_REQUIRE(h && params, "null handle/params");
+  MB200_TRY(check_bodies(bodies));
+  MB200_TRY(require_device());
+  cudaStream_t st = as_stream(stream);
+  const long long launches0 = g_launches.load();
+  int rebuilt = 0;
+  MB200_TRY(links_generate(st, h, bodies, params->force_rebuild, &rebuilt));
+  return step_core(h, st, bodies, params, F_ext, T_ext, F_col, T_col, U_out, W_out, rebuilt, launches0, nullptr, stats_h);
 }
 
 // Host-buffer entry point: H2D of this step's inputs, the device step, D2H of the advanced state and outputs.

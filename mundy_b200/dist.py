@@ -1,0 +1,146 @@
+"""Multi-GPU host side: Hilbert-curve ordering of the bodies, the NCCL communicator, the distributed step wrapper, and a
+numpy statement of the decomposition plan (what the device code in csrc/dist_step.cu builds), used by the CPU tests.
+
+Decomposition (include/mundy_b200.h "Multi-GPU"): bodies are sorted along a 3-D Hilbert curve of their centres once
+(`hilbert_order`); rank r owns the contiguous block [r n/W, (r+1) n/W) of that order; every rank keeps a replica of the
+body arrays. The reference decomposes with stk::balance RCB and never names a curve index (mundy/math/Hilbert.hpp
+is a curve *generator*); its Hilbert generator and this index function describe the same family of curves: consecutive
+indices are face-adjacent lattice cells (tests/test_dist_cpu.py).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi as capi
+from ._capi import check, lib
+
+
+# ---- Hilbert ordering (Skilling, "Programming the Hilbert curve", AIP Conf. Proc. 707, 2004: transpose form) ---------
+def hilbert_index(cells, bits):
+    """cells: (n, 3) integer lattice coordinates in [0, 2^bits). Returns the uint64 Hilbert index of every cell."""
+    X = np.array(cells, dtype=np.uint64).T.copy()  # (3, n)
+    n = 3
+    M = np.uint64(1) << np.uint64(bits - 1)
+    Q = M
+    while Q > np.uint64(1):  # inverse undo excess work
+        P = Q - np.uint64(1)
+        for i in range(n):
+            hit = (X[i] & Q) != 0
+            X[0] = np.where(hit, X[0] ^ P, X[0])          # invert low bits of X[0]
+            t = (X[0] ^ X[i]) & P                          # exchange low bits of X[0] and X[i]
+            X[0] = np.where(hit, X[0], X[0] ^ t)
+            X[i] = np.where(hit, X[i], X[i] ^ t)
+        Q >>= np.uint64(1)
+    for i in range(1, n):  # Gray encode
+        X[i] ^= X[i - 1]
+    t = np.zeros_like(X[0])
+    Q = M
+    while Q > np.uint64(1):
+        t = np.where((X[n - 1] & Q) != 0, t ^ (Q - np.uint64(1)), t)
+        Q >>= np.uint64(1)
+    for i in range(n):
+        X[i] ^= t
+    # interleave the transposed bits: bit b of X[i] -> bit (b * 3 + (2 - i)) of the index
+    h = np.zeros(X.shape[1], dtype=np.uint64)
+    for b in range(bits - 1, -1, -1):
+        for i in range(n):
+            h = (h << np.uint64(1)) | ((X[i] >> np.uint64(b)) & np.uint64(1))
+    return h
+
+
+def hilbert_order(center, bits=10):
+    """Permutation that sorts the bodies along the Hilbert curve of their centres (2^bits cells per axis)."""
+    center = np.asarray(center, dtype=np.float64)
+    lo, hi = center.min(axis=0), center.max(axis=0)
+    span = float(np.max(hi - lo))
+    span = span if span > 0 else 1.0
+    cells = np.minimum(((center - lo) / span * (1 << bits)).astype(np.int64), (1 << bits) - 1)
+    # axes passed as (z, y, x): the curve then starts along x like the reference's generator
+    # (mundy/math/tests/unit_tests/UnitTestHilbert.cpp:47-66, the 2^3 golden order)
+    return np.argsort(hilbert_index(cells[:, ::-1], bits), kind="stable")
+
+
+def reorder(workload, order):
+    """Apply a body permutation to every per-body array of a workload dict."""
+    n = len(workload["radius"])
+    return {k: (v[order] if isinstance(v, np.ndarray) and v.shape[:1] == (n,) else v) for k, v in workload.items()}
+
+
+def owned_range(n, world, rank):
+    assert n % world == 0, "the number of bodies must be a multiple of the world size"
+    m = n // world
+    return rank * m, (rank + 1) * m
+
+
+# ---- the decomposition plan, in numpy (specification of csrc/dist_step.cu; O(n_local^2)-free but host-speed) ---------
+def plan(center, S, world, rank, find_pairs):
+    """center (n,3), S (n,) search radii of ALL bodies. find_pairs(center_local, S_local) -> sorted (m,2) int pairs i<j.
+    Returns dict(gidx, owned, links (global ids, with >= 1 owned end), counted, send {peer: gids}, recv {peer: gids})."""
+    n = len(S)
+    o0, o1 = owned_range(n, world, rank)
+    own = np.zeros(n, dtype=bool)
+    own[o0:o1] = True
+    lo, hi = center[o0:o1].min(axis=0), center[o0:o1].max(axis=0)
+    reach = ((S + S[o0:o1].max()) * (1.0 + 1e-9))[:, None]
+    near = np.all((center >= lo - reach) & (center <= hi + reach), axis=1)
+    gidx = np.nonzero(own | near)[0]                      # ascending global index: local order = global order
+    pairs = find_pairs(center[gidx], S[gidx])
+    gi, gj = gidx[pairs[:, 0]], gidx[pairs[:, 1]]
+    keep = own[gi] | own[gj]                              # ghost-ghost links belong to other ranks
+    gi, gj = gi[keep], gj[keep]
+    m = n // world
+    oi, oj = gi // m, gj // m
+    counted = oi == rank                                  # gi < gj: the owner of the lower index counts the link
+    cut = oi != oj
+    send, recv = {}, {}
+    for p in range(world):
+        if p == rank:
+            continue
+        s = np.concatenate([gi[cut & (oi == rank) & (oj == p)], gj[cut & (oj == rank) & (oi == p)]])
+        r = np.concatenate([gj[cut & (oi == rank) & (oj == p)], gi[cut & (oj == rank) & (oi == p)]])
+        send[p], recv[p] = np.unique(s), np.unique(r)
+    return dict(gidx=gidx, owned=own[gidx], links=np.stack([gi, gj], axis=1), counted=counted, send=send, recv=recv)
+
+
+# ---- communicator and distributed step --------------------------------------------------------------------------------
+class Comm:
+    """NCCL communicator of libmundy_b200 (its own ncclComm; the unique id travels over torch.distributed)."""
+
+    def __init__(self, device=None):
+        import torch
+        import torch.distributed as dist
+
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        buf = C.create_string_buffer(128)
+        if self.rank == 0:
+            check(lib.mb200_comm_get_unique_id(buf), "comm_get_unique_id")
+        if self.world > 1:
+            dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+            t = torch.tensor(list(buf.raw), dtype=torch.uint8, device=dev if dist.get_backend() == "nccl" else "cpu")
+            dist.broadcast(t, 0)
+            buf = C.create_string_buffer(bytes(t.cpu().tolist()), 128)
+        self._h = C.c_void_p()
+        check(lib.mb200_comm_create(C.byref(self._h), self.world, self.rank, buf), "comm_create")
+
+    def __del__(self):
+        if getattr(self, "_h", None) and lib is not None:
+            lib.mb200_comm_destroy(self._h)
+            self._h = None
+
+
+def step_dist(links, comm, bodies, viscosity, dt, tol, max_iters, fixed_iters=-1, force_rebuild=False, F_ext=None,
+              T_ext=None, F_col=None, U_out=None, throw_on_max_iters=False):
+    """One distributed collision step on the replicated global body set (`bodies` = ops.make_bodies of ALL bodies)."""
+    from .ops import _f64, _stream
+    params = capi.StepParams(viscosity, dt, tol, max_iters, fixed_iters, int(throw_on_max_iters), int(force_rebuild))
+    stats = capi.StepStats()
+    check(lib.mb200_collision_step_dist(links._h, comm._h, _stream(), C.byref(bodies), C.byref(params), _f64(F_ext),
+                                        _f64(T_ext), _f64(F_col), _f64(U_out), C.byref(stats)), "collision_step_dist")
+    return stats
+
+
+def local_counts(links):
+    a, b = C.c_int64(0), C.c_int64(0)
+    check(lib.mb200_dist_local_counts(links._h, C.byref(a), C.byref(b)), "dist_local_counts")
+    return a.value, b.value

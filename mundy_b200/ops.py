@@ -274,7 +274,8 @@ def kernel_launch_count():
     return lib.mb200_kernel_launch_count()
 
 
-STAGES = ("trigger", "broadphase", "pack", "narrow", "lcp_setup", "lcp_body", "lcp_rate", "euler")
+STAGES = ("trigger", "broadphase", "pack", "narrow", "lcp_setup", "lcp_body", "lcp_rate", "euler", "lcp_comm",
+          "state_comm")
 
 
 def profile_enable(on=True):
