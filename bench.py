@@ -164,7 +164,9 @@ def workload_config(args, n):
             "bodies_per_gpu": n, "mu": MU, "dt": DT, "tol": TOL, "max_iters": MAX_ITERS, "search_buffer": BUFFER,
             "search_filter": "shape_distance<=2*buffer" if args.filter == "shape" else "none (all bounding-sphere candidates)",
             "forcing": "attractive ABC flow", "l2": "inputs larger than L2 (contact arrays >= 400 MB per GPU)",
-            "parallelism": "1 GPU" if args.gpus == 1 else f"{args.gpus} ranks, one independent sub-box each"}
+            "parallelism": "1 GPU" if args.gpus == 1 else
+            f"{args.gpus} ranks, one box of {args.gpus}x{n} bodies, Hilbert-curve blocks, ghost velocity halo (NCCL send/recv) "
+            "+ all-gathered solver sums per iteration, state all-gather per step"}
 
 
 # ---- B200 arm ---------------------------------------------------------------------------------------------------------
@@ -186,8 +188,18 @@ def run_b200(args):
 
     n = args.bodies
     filt = args.filter == "shape"
-    w = wl.rods(n, phi=PHI, radius=RADIUS, length=LENGTH, seed=3 + rank)
     dev = torch.device("cuda", local)
+    comm = None
+    if world > 1:
+        # weak scaling: world * n bodies in one box at the same density, ordered along the Hilbert curve; every rank
+        # builds the same replica (same seed) and owns one contiguous block of n bodies (mundy_b200/dist.py)
+        from mundy_b200 import dist as mbd
+        w = wl.rods(n * world, phi=PHI, radius=RADIUS, length=LENGTH, seed=3)
+        w = mbd.reorder(w, mbd.hilbert_order(w["center"]))
+        comm = mbd.Comm(dev)
+    else:
+        w = wl.rods(n, phi=PHI, radius=RADIUS, length=LENGTH, seed=3)
+    ntot = len(w["radius"])
 
     def to_dev(x, dtype=torch.float64):
         return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype, device=dev)
@@ -195,7 +207,7 @@ def run_b200(args):
     c, q = to_dev(w["center"]), to_dev(w["quat"])
     r, L, kind = to_dev(w["radius"]), to_dev(w["length"]), to_dev(w["kind"], torch.int32)
     bodies = ops.make_bodies(c, r, q, L, kind)
-    F = torch.zeros((n, 3), dtype=torch.float64, device=dev)
+    F = torch.zeros((ntot, 3), dtype=torch.float64, device=dev)
     links = ops.NeighborLinks().set_search_buffer(BUFFER)
     if filt:
         links.set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
@@ -205,8 +217,14 @@ def run_b200(args):
     def step():
         F.zero_()
         ops.abc_flow_force(c, F)
-        st = links.step(bodies, MU, DT, TOL, MAX_ITERS, F_ext=F)
+        if comm is None:
+            st = links.step(bodies, MU, DT, TOL, MAX_ITERS, F_ext=F)
+        else:
+            st = mbd.step_dist(links, comm, bodies, MU, DT, TOL, MAX_ITERS, F_ext=F)
         log.append((st.lcp.ite_count, st.num_links, st.rebuilt, st.lcp.converged))
+        if os.environ.get("MB200_BENCH_VERBOSE"):
+            print(f"[rank {rank}] step {len(log)}: iters {st.lcp.ite_count} links {st.num_links} rebuilt {st.rebuilt} "
+                  f"res {st.lcp.max_abs_projected_sep:.3e} t {time.perf_counter():.1f}", file=sys.stderr, flush=True)
         return st
 
     def barrier():
@@ -242,11 +260,42 @@ def run_b200(args):
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    value = n * world * args.steps / (ms * 1e-3)
+    value = ntot * args.steps / (ms * 1e-3)
 
     # ---- e2e: host arrays through mb200_collision_step_host ---------------------------------------------------------
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and comm is not None:
+        # every rank keeps its OWNED block in pinned host memory: each step uploads it (centres, quaternions, forcing),
+        # all-gathers the blocks into the device replicas, runs the distributed step and reads the owned block back
+        o0 = rank * n
+        hc, hq, hF = (x[o0:o0 + n].cpu().pin_memory() for x in (c, q, F))
+        dc, dq, dF = (torch.empty_like(x[o0:o0 + n]) for x in (c, q, F))
+        e2e_steps = max(3, min(args.steps, 10))
+
+        def host_step():
+            for d_, h_, g_ in ((dc, hc, c), (dq, hq, q), (dF, hF, F)):
+                d_.copy_(h_, non_blocking=True)
+                dist.all_gather_into_tensor(g_, d_)
+            mbd.step_dist(links, comm, bodies, MU, DT, TOL, MAX_ITERS, F_ext=F)
+            hc.copy_(c[o0:o0 + n], non_blocking=True)
+            hq.copy_(q[o0:o0 + n], non_blocking=True)
+            torch.cuda.synchronize()
+
+        host_step()
+        barrier()
+        ev0.record()
+        for _ in range(e2e_steps):
+            host_step()
+        ev1.record()
+        barrier()
+        t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e = float(t.item())
+        e2e = {"value": ntot * e2e_steps / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (3 + 4 + 3) * 8 * ntot,
+               "d2h_bytes_per_step": (3 + 4) * 8 * ntot, "steps": e2e_steps, "ms_per_step": ms_e / e2e_steps,
+               "api": "per rank: pinned owned block -> H2D -> all-gather into the replicas -> mb200_collision_step_dist "
+                      "-> D2H of the owned block (bytes summed over ranks)"}
+    elif not args.no_e2e:
         hc, hq = c.cpu().pin_memory(), q.cpu().pin_memory()
         hr, hL, hk = r.cpu().pin_memory(), L.cpu().pin_memory(), kind.cpu().pin_memory()
         hF = F.cpu().pin_memory()  # forcing sampled at the current positions, kept for the e2e steps
@@ -291,7 +340,8 @@ def run_b200(args):
     stage_out = {}
     if stages:
         # algorithmic bytes per launch (DESIGN.md "Kernels"): C contacts, n bodies, 6-DOF
-        alg = {"lcp_rate": 128.0 * C + 64.0 * n, "lcp_body": 120.0 * C + 104.0 * n}
+        nloc = mbd.local_counts(links)[0] if comm is not None else n  # bodies this rank works on (owned + ghosts)
+        alg = {"lcp_rate": 128.0 * C + 64.0 * nloc, "lcp_body": 120.0 * C + 104.0 * nloc}
         for name, (tot_ms, cnt) in stages.items():
             stage_out[name] = {"ms_total": round(tot_ms, 4), "regions": cnt}
             if name in alg and cnt > 0:
@@ -308,7 +358,7 @@ def run_b200(args):
             it_ms = sum(stages[k][0] for k in ("lcp_rate", "lcp_body"))
             its = stages["lcp_rate"][1]  # operator applications (one body pass + one contact pass each)
             if its > 0:
-                it_bytes = 120.0 * C + 240.0 * n  # fused-ideal bytes of one rod BBPGD iteration
+                it_bytes = 120.0 * C + 240.0 * nloc  # fused-ideal bytes of one rod BBPGD iteration
                 roofline["lcp_iteration"] = {"alg_bytes": it_bytes, "avg_us": 1e3 * it_ms / its,
                                              "gbs": it_bytes / (it_ms / its * 1e-3) / 1e9,
                                              "frac": it_bytes / (it_ms / its * 1e-3) / 1e9 / peak}
@@ -329,6 +379,10 @@ def run_b200(args):
         "lcp_iters_per_step": [x[0] for x in tlog], "links_per_step": int(C), "rebuilds": sum(x[2] for x in tlog),
         "all_converged": all(x[3] for x in tlog), "stages": stage_out, "prep_steps": args.prep,
     }
+    if comm is not None:
+        nl, ng = mbd.local_counts(links)
+        line["dist"] = {"rank0_local_bodies": nl, "rank0_ghost_rows": ng, "owned_per_rank": n,
+                        "note": "links_per_step, stages and roofline are rank 0's"}
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
