@@ -351,8 +351,14 @@ def run_b200(args):
         tot_ms, cnt = stages[dom]
         if cnt > 0:
             achieved = alg[dom] / (tot_ms / cnt * 1e-3) / 1e9
+            traffic = None  # DRAM bytes per launch from the committed ncu capture (same workload), if there is one
+            try:
+                if n == 1_000_000 and args.filter == "shape":
+                    traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(dom)
+            except (OSError, ValueError):
+                pass
             roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                         "launches": cnt, "avg_us": 1e3 * tot_ms / cnt,
                         "share_of_step": tot_ms / ms}
             it_ms = sum(stages[k][0] for k in ("lcp_rate", "lcp_body"))
