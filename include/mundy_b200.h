@@ -134,6 +134,18 @@ int mb200_neighbor_links_destroy(mb200_neighbor_links* h);
 /* Builder setters (set_search_buffer :455, set_search_filter :441, set_sort_search_results :427). */
 int mb200_neighbor_links_set_search_buffer(mb200_neighbor_links* h, double buffer);
 int mb200_neighbor_links_set_search_filter(mb200_neighbor_links* h, int filter);
+/* Orthorhombic periodic box (BASELINE configs[1] "periodic box"). cell_size_h = HOST array of the
+ * three cell edge lengths; an entry <= 0 leaves that axis free; NULL switches periodicity off (the default).
+ * All three axes periodic = geom::PeriodicScaledMetric (mundy/geom/src/mundy_geom/periodicity.hpp:743-845), a subset =
+ * PeriodicMetricX / Y / XY / YZ (:335-741). With a periodic box
+ *   - the candidate predicate measures the centre separation with metric.sep (minimum image, :814-818):
+ *     |sep(c_i, c_j)|^2 <= (S_i + S_j)^2; each unordered pair is one link (its nearest image);
+ *   - the narrow phase and the shape filter evaluate geom::distance(body_i, unwrap_points_to_ref(body_j, metric, c_i))
+ *     (:1487-1516), i = the lower caller index; arms of j are relative to its unwrapped centre;
+ *   - the rebuild trigger measures metric.sep(point at build time, point now);
+ *   - centres are NOT wrapped by the step (trajectories stay continuous; wrap with mb200_periodic_wrap when wanted).
+ * The cell list tiles each periodic axis with whole cells and wraps its neighbour walk, so no ghost images are made. */
+int mb200_neighbor_links_set_periodic(mb200_neighbor_links* h, const double* cell_size_h);
 /* generate() :510-543. Rebuilds when never built, when n changed, when force != 0, or when some body moved more than
  * half the buffer since the last build (:603-615). *rebuilt_h (host) receives 1/0. Synchronises the stream. */
 int mb200_neighbor_links_generate(mb200_neighbor_links* h, mb200_stream stream, const mb200_bodies* bodies, int force,
@@ -147,6 +159,26 @@ int mb200_neighbor_links_get_pairs(mb200_neighbor_links* h, mb200_stream stream,
  * *count_h (host) receives the number found even when it exceeds capacity (then MB200_ERR_CAPACITY). */
 int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, const double* search_radius,
                        int32_t* pairs_out, int64_t capacity, int64_t* count_h);
+
+/* The same with a periodic box (cell_size_h as in mb200_neighbor_links_set_periodic). */
+int mb200_search_pairs_periodic(mb200_stream stream, int64_t n, const double* center, const double* search_radius,
+                                const double* cell_size_h, int32_t* pairs_out, int64_t capacity, int64_t* count_h);
+/* mb200_narrow_phase with a periodic box: body j of every pair is unwrapped to the centre of body i first. */
+int mb200_narrow_phase_periodic(mb200_stream stream, const mb200_bodies* bodies, int64_t npairs, const int32_t* pairs,
+                                const double* cell_size_h, double* phi, double* normal, double* arm_i, double* arm_j);
+
+/* Periodic metric leaves, batched (mundy/geom/src/mundy_geom/periodicity.hpp; every array [3n]; cell_size_h HOST[3]):
+ *   sep[k]  = metric.sep(p1[k], p2[k])                          :814-818  minimum-image separation vector
+ *   out[k]  = metric.wrap(p[k])                                 :821-824  into [0, L) per periodic axis
+ *   out[k]  = unwrap_points_to_ref(p[k], metric, ref[k])        :1333-1339 (points, sphere / spherocylinder centres)
+ *   (start_out, end_out)[k] = unwrap_points_to_ref(LineSegment(start[k], end[k]), metric, ref[k])   :1368-1382 */
+int mb200_periodic_sep(mb200_stream stream, int64_t n, const double* cell_size_h, const double* p1, const double* p2,
+                       double* sep);
+int mb200_periodic_wrap(mb200_stream stream, int64_t n, const double* cell_size_h, const double* p, double* out);
+int mb200_periodic_unwrap_points(mb200_stream stream, int64_t n, const double* cell_size_h, const double* p,
+                                 const double* ref, double* out);
+int mb200_periodic_unwrap_segments(mb200_stream stream, int64_t n, const double* cell_size_h, const double* start,
+                                   const double* end, const double* ref, double* start_out, double* end_out);
 
 /* ---------------------------------------------------------------------------------------------------------------
  * D. Matrix-free contact operator (there is no assembled Jacobian in the reference).

@@ -9,6 +9,7 @@
 // The optional shape-distance search filter (GenNeighborLinkers.hpp:116-200 SearchFilter) is fused into the same passes.
 #include <algorithm>
 #include <cmath>
+#include <type_traits>
 #include <vector>
 
 #include "links.cuh"
@@ -22,9 +23,11 @@ constexpr int kMaxBitsPerAxis = 8;  // dense cell table of at most 2^24 entries
 
 struct GridParams {
   double lo[3];
-  double h;
+  double h[3];
   int nc[3];
-  int bits;  // per axis
+  int bits;       // per axis
+  int per[3];     // periodic axis: cells tile [0, L) exactly, h = L / nc, neighbour cells wrap around
+  double inv[3];  // 1 / L on periodic axes
 };
 
 __device__ __host__ inline uint32_t spread3(uint32_t v) {  // 10 bits -> every third bit
@@ -40,9 +43,15 @@ __device__ __host__ inline uint32_t morton3(uint32_t cx, uint32_t cy, uint32_t c
   return spread3(cx) | (spread3(cy) << 1) | (spread3(cz) << 2);
 }
 
-__device__ inline int cell_coord(double x, double lo, double h, int nc) {
-  const int v = static_cast<int>(floor((x - lo) / h));
-  return min(max(v, 0), nc - 1);
+__device__ inline int cell_coord(double x, const GridParams& gp, int d) {
+  int v;
+  if (gp.per[d]) {  // cell of the wrapped fractional coordinate (any periodic image gives the same cell)
+    const double f = x * gp.inv[d];
+    v = static_cast<int>((f - floor(f)) * gp.nc[d]);
+  } else {
+    v = static_cast<int>(floor((x - gp.lo[d]) / gp.h[d]));
+  }
+  return min(max(v, 0), gp.nc[d] - 1);
 }
 
 // Search spheres in the caller's order + per-CTA bounds partials (min xyz, max xyz, max S).
@@ -89,8 +98,7 @@ __global__ void __launch_bounds__(256) cell_keys_kernel(int64_t n, const D4* __r
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const D4 s = ldg256(sr + i);
-  keys[i] = morton3(cell_coord(s.x, gp.lo[0], gp.h, gp.nc[0]), cell_coord(s.y, gp.lo[1], gp.h, gp.nc[1]),
-                    cell_coord(s.z, gp.lo[2], gp.h, gp.nc[2]));
+  keys[i] = morton3(cell_coord(s.x, gp, 0), cell_coord(s.y, gp, 1), cell_coord(s.z, gp, 2));
   vals[i] = static_cast<uint32_t>(i);
 }
 
@@ -118,13 +126,15 @@ __global__ void __launch_bounds__(256) cell_ranges_kernel(int64_t n, const uint3
 // The candidates of the <= 27 neighbour cells with key >= own key are walked as ONE flattened index range in
 // ascending key order (= ascending j): 64 candidates per trip, both 256-bit record loads of a lane issued before the
 // first test, exact fp64 predicate, warp ballot + popc compaction.
-template <bool FILL, bool FILTER>
+// PER: periodic box. Neighbour cells wrap around on periodic axes (an axis with fewer than three cells visits each of
+// its cells once), the predicate uses the minimum-image separation and the shape filter unwraps the second body.
+template <bool FILL, bool FILTER, bool PER>
 __global__ void __launch_bounds__(256)
     find_pairs_kernel(int64_t n, const D4* __restrict__ sr, const D4* __restrict__ b0, const D4* __restrict__ b1,
                       const uint32_t* __restrict__ perm, const int2* __restrict__ cell_range, GridParams gp,
                       double cutoff, uint32_t* __restrict__ counts, const int64_t* __restrict__ rowptr,
                       int2* __restrict__ pairs, int32_t* __restrict__ slots, int slot_cap,
-                      const uint8_t* __restrict__ own) {
+                      const uint8_t* __restrict__ own, Periodic P) {
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
   const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
@@ -149,16 +159,29 @@ __global__ void __launch_bounds__(256)
     b1i = ldg256(b1 + i);
     pi = perm[i];
   }
-  const int cx = cell_coord(si.x, gp.lo[0], gp.h, gp.nc[0]);
-  const int cy = cell_coord(si.y, gp.lo[1], gp.h, gp.nc[1]);
-  const int cz = cell_coord(si.z, gp.lo[2], gp.h, gp.nc[2]);
+  const int cx = cell_coord(si.x, gp, 0);
+  const int cy = cell_coord(si.y, gp, 1);
+  const int cz = cell_coord(si.z, gp, 2);
   const uint32_t my_key = morton3(cx, cy, cz);
   // lane l < 27 owns neighbour cell l
   uint32_t nkey = 0xffffffffu;
   int beg = 0, len = 0;
   if (lane < 27) {
-    const int x = cx + (lane % 3) - 1, y = cy + ((lane / 3) % 3) - 1, z = cz + (lane / 9) - 1;
-    if (x >= 0 && y >= 0 && z >= 0 && x < gp.nc[0] && y < gp.nc[1] && z < gp.nc[2]) {
+    int x = cx + (lane % 3) - 1, y = cy + ((lane / 3) % 3) - 1, z = cz + (lane / 9) - 1;
+    bool inside = true;
+    if (PER) {
+      const int off[3] = {(lane % 3) - 1, ((lane / 3) % 3) - 1, (lane / 9) - 1};
+      int* xyz[3] = {&x, &y, &z};
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        if (gp.per[d]) {
+          // offsets that would revisit a cell of a short axis are dropped: -1 needs two cells, +1 needs three
+          inside = inside && (off[d] == 0 || (off[d] < 0 ? gp.nc[d] >= 2 : gp.nc[d] >= 3));
+          *xyz[d] = (*xyz[d] + gp.nc[d]) % gp.nc[d];
+        }
+      }
+    }
+    if (inside && x >= 0 && y >= 0 && z >= 0 && x < gp.nc[0] && y < gp.nc[1] && z < gp.nc[2]) {
       const uint32_t k = morton3(x, y, z);
       if (k >= my_key) {  // bodies with a smaller key have a smaller index: never j > i
         const int2 r = __ldg(cell_range + k);
@@ -222,8 +245,12 @@ __global__ void __launch_bounds__(256)
     if (j >= 0) {
       // evaluate in the caller's (i<j) order so that the decision is bit-identical to the reference order
       const D4 b0j = ldg256(b0 + j), b1j = ldg256(b1 + j);
-      const PairGeom g = (pi < perm[j]) ? pair_geometry<true>(b0i, b1i, b0j, b1j)
-                                        : pair_geometry<true>(b0j, b1j, b0i, b1i);
+      PairGeom g;
+      if (PER)
+        g = (pi < perm[j]) ? pair_geometry<true>(b0i, b1i, unwrap_to(P, b0i, b0j), b1j)
+                           : pair_geometry<true>(b0j, b1j, unwrap_to(P, b0j, b0i), b1i);
+      else
+        g = (pi < perm[j]) ? pair_geometry<true>(b0i, b1i, b0j, b1j) : pair_geometry<true>(b0j, b1j, b0i, b1i);
       keep = g.sep <= cutoff;
     }
     emit(keep, j);
@@ -243,8 +270,8 @@ __global__ void __launch_bounds__(256)
     D4 sa{0, 0, 0, 0}, sb{0, 0, 0, 0};
     if (ja >= 0) sa = ldg256(sr + ja);
     if (jb >= 0) sb = ldg256(sr + jb);
-    const bool ka = (ja >= 0) && is_candidate(si, sa) && (own_i || own[ja]);
-    const bool kb = (jb >= 0) && is_candidate(si, sb) && (own_i || own[jb]);
+    const bool ka = (ja >= 0) && (PER ? is_candidate_periodic(P, si, sa) : is_candidate(si, sa)) && (own_i || own[ja]);
+    const bool kb = (jb >= 0) && (PER ? is_candidate_periodic(P, si, sb) : is_candidate(si, sb)) && (own_i || own[jb]);
     if (FILTER) {
       const uint32_t ma = __ballot_sync(0xffffffffu, ka), mb = __ballot_sync(0xffffffffu, kb);
       if (ka) q[qn + __popc(ma & lt_mask)] = ja;
@@ -270,7 +297,7 @@ namespace {
 __global__ void __launch_bounds__(256)
     moved_kernel(int64_t n, const double* __restrict__ center, const double* __restrict__ ref_center,
                  const double* __restrict__ quat, const double* __restrict__ length, const int32_t* __restrict__ kind,
-                 const D4* __restrict__ ref_b1, double thresh, int32_t* __restrict__ flag) {
+                 const D4* __restrict__ ref_b1, double thresh, int32_t* __restrict__ flag, Periodic P) {
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const V3 c = ld3(center, i), c0 = ld3(ref_center, i);
@@ -279,11 +306,13 @@ __global__ void __launch_bounds__(256)
     const D4 r = ldg256(ref_b1 + i);
     const V3 h0{r.x, r.y, r.z};
     const V3 h = (0.5 * length[i]) * qrot(ldq(quat, i), V3{0.0, 0.0, 1.0});
-    const V3 da = (c - h) - (c0 - h0), db = (c + h) - (c0 + h0);
+    // periodic box: displacement = metric.sep(point at build time, point now) (a wrapped centre has not moved)
+    const V3 da = P.any ? periodic_sep(P, c0 - h0, c - h) : (c - h) - (c0 - h0);
+    const V3 db = P.any ? periodic_sep(P, c0 + h0, c + h) : (c + h) - (c0 + h0);
     moved = sqrt(da.x * da.x + da.y * da.y + da.z * da.z) > thresh || sqrt(db.x * db.x + db.y * db.y + db.z * db.z) > thresh;
   } else {
-    const double dx = c.x - c0.x, dy = c.y - c0.y, dz = c.z - c0.z;
-    moved = sqrt(dx * dx + dy * dy + dz * dz) > thresh;
+    const V3 dd = P.any ? periodic_sep(P, c0, c) : V3{c.x - c0.x, c.y - c0.y, c.z - c0.z};
+    moved = sqrt(dd.x * dd.x + dd.y * dd.y + dd.z * dd.z) > thresh;
   }
   if (moved) *flag = 1;
 }
@@ -361,9 +390,11 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   // floor() binning can never separate a candidate pair by more than one cell
   double edge = 2.0 * smax * (1.0 + 1e-9);
   if (!(edge > 0.0)) edge = 1.0;
+  const Periodic P = h->periodic;
   for (;;) {
     bool ok = true;
     for (int d = 0; d < 3; ++d) {
+      if (P.on[d]) continue;
       const double cells = std::floor((hi[d] - lo[d]) / edge) + 1.0;
       ok = ok && cells <= double(1 << kMaxBitsPerAxis);
       gp.nc[d] = ok ? static_cast<int>(cells) : 0;
@@ -371,8 +402,19 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
     if (ok) break;
     edge *= 2.0;  // larger cells stay correct, only slower
   }
-  gp.h = edge;
-  for (int d = 0; d < 3; ++d) gp.lo[d] = lo[d];
+  for (int d = 0; d < 3; ++d) {
+    gp.per[d] = P.on[d];
+    gp.inv[d] = P.inv[d];
+    if (P.on[d]) {  // whole cells tile the period: nc = floor(L / edge) cells of edge L / nc >= edge
+      const double cells = std::floor(P.L[d] / edge);
+      gp.nc[d] = static_cast<int>(std::min(std::max(cells, 1.0), double(1 << kMaxBitsPerAxis)));
+      gp.h[d] = P.L[d] / gp.nc[d];
+      gp.lo[d] = 0.0;
+    } else {
+      gp.h[d] = edge;
+      gp.lo[d] = lo[d];
+    }
+  }
   gp.bits = bits_for(std::max(gp.nc[0], std::max(gp.nc[1], gp.nc[2])));
   const int key_bits = 3 * gp.bits;
   const int64_t table = int64_t(1) << key_bits;
@@ -419,12 +461,22 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   MB200_TRY(rowptr.alloc(n + 1, st));
   const double cutoff = 2.0 * h->buffer;
   const int pgrid = grid_for(n * 32, 256);
-  if (filter)
-    find_pairs_kernel<false, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
-                                                         counts.p, nullptr, nullptr, slots.p, slot_cap, own_s.p);
-  else
-    find_pairs_kernel<false, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
-                                                          cutoff, counts.p, nullptr, nullptr, slots.p, slot_cap, own_s.p);
+  auto launch_find = [&](auto fill_tag, const int64_t* rp, int2* out) {
+    constexpr bool FILL = decltype(fill_tag)::value;
+    uint32_t* cnt = FILL ? nullptr : counts.p;
+#define MB200_FIND(FILTER, PER)                                                                                      \
+  find_pairs_kernel<FILL, FILTER, PER><<<pgrid, 256, 0, st>>>(n, sr_s.p, FILTER ? b0s.p : nullptr,                   \
+                                                              FILTER ? b1s.p : nullptr, FILTER ? h->perm.p : nullptr, \
+                                                              cell_range.p, gp, cutoff, cnt, rp, out, slots.p,       \
+                                                              slot_cap, own_s.p, P)
+    if (filter) {
+      if (P.any) MB200_FIND(true, true); else MB200_FIND(true, false);
+    } else {
+      if (P.any) MB200_FIND(false, true); else MB200_FIND(false, false);
+    }
+#undef MB200_FIND
+  };
+  launch_find(std::false_type{}, nullptr, nullptr);
   MB200_LAUNCHED();
   MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, rowptr.p));
   int64_t total = 0;
@@ -438,12 +490,7 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   MB200_TRY(h->pairs.reserve(2 * total + 2));
   if (total > 0) {
     int2* out = reinterpret_cast<int2*>(h->pairs.p);
-    if (filter)
-      find_pairs_kernel<true, true><<<pgrid, 256, 0, st>>>(n, sr_s.p, b0s.p, b1s.p, h->perm.p, cell_range.p, gp, cutoff,
-                                                          nullptr, rowptr.p, out, slots.p, slot_cap, own_s.p);
-    else
-      find_pairs_kernel<true, false><<<pgrid, 256, 0, st>>>(n, sr_s.p, nullptr, nullptr, nullptr, cell_range.p, gp,
-                                                           cutoff, nullptr, rowptr.p, out, slots.p, slot_cap, own_s.p);
+    launch_find(std::true_type{}, rowptr.p, out);
     MB200_LAUNCHED();
   }
   // 5. body-major incidence lists for the contact operator
@@ -457,7 +504,8 @@ int links_moved_flag(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodie
   if (b->n == 0) return MB200_OK;
   const bool shape = h->filter == MB200_FILTER_SHAPE_DISTANCE && h->rods;
   moved_kernel<<<grid_for(b->n, 256), 256, 0, st>>>(b->n, b->center, h->ref_center.p, b->quat, b->length, b->kind,
-                                                   shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p);
+                                                   shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p,
+                                                   h->periodic);
   MB200_LAUNCHED();
   return MB200_OK;
 }
@@ -470,7 +518,8 @@ int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies*
     MB200_CUDA(cudaMemsetAsync(h->flag.p, 0, sizeof(int32_t), st));
     const bool shape = h->filter == MB200_FILTER_SHAPE_DISTANCE && h->rods;
     moved_kernel<<<grid_for(b->n, 256), 256, 0, st>>>(b->n, b->center, h->ref_center.p, b->quat, b->length, b->kind,
-                                                     shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p);
+                                                     shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p,
+                                                   h->periodic);
     MB200_LAUNCHED();
     int32_t moved = 0;
     MB200_CUDA(cudaMemcpyAsync(&moved, h->flag.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));

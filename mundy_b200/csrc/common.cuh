@@ -198,6 +198,56 @@ __device__ inline void st256(D4* p, const D4& v) {
   asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w) : "memory");
 }
 
+// Orthorhombic periodic metric: geom::PeriodicScaledMetric (mundy/geom/src/mundy_geom/periodicity.hpp:743-845) when all
+// three axes are periodic, PeriodicMetricX / Y / XY / YZ (:335-741) when only some are (their free axes carry scale 1
+// and are not rounded, which is the identity in fp64). Passed to kernels by value.
+struct Periodic {
+  double L[3];    // scale_
+  double inv[3];  // scale_inv_ = 1.0 / scale_
+  int on[3];
+  int any;
+};
+inline Periodic make_periodic(const double* cell_size) {  // cell_size[d] <= 0 (or NULL): free axis
+  Periodic P{};
+  for (int d = 0; d < 3; ++d) {
+    P.on[d] = cell_size && cell_size[d] > 0.0;
+    P.L[d] = P.on[d] ? cell_size[d] : 1.0;
+    P.inv[d] = 1.0 / P.L[d];
+    P.any |= P.on[d];
+  }
+  return P;
+}
+// frac_minimum_image<int64_t> (:799-803): x - Scalar(int64(round(x))), round = half away from zero.
+__host__ __device__ inline double frac_min_image(double x) { return x - static_cast<double>(static_cast<long long>(round(x))); }
+// impl::safe_unit_mod1<int64_t> (:140-150)
+__host__ __device__ inline double safe_unit_mod1(double s) {
+  const double k = static_cast<double>(static_cast<long long>(floor(s)));
+  double t = s - k;
+  if (fabs(t - 1.0) < kZeroTol) t = 0.0;
+  return t;
+}
+// metric.sep(p1, p2) (:814-818): from_fractional(frac_minimum_image(to_fractional(p2 - p1)))
+__host__ __device__ inline V3 periodic_sep(const Periodic& P, const V3& p1, const V3& p2) {
+  V3 d = p2 - p1;
+  if (P.on[0]) d.x = P.L[0] * frac_min_image(P.inv[0] * d.x);
+  if (P.on[1]) d.y = P.L[1] * frac_min_image(P.inv[1] * d.y);
+  if (P.on[2]) d.z = P.L[2] * frac_min_image(P.inv[2] * d.z);
+  return d;
+}
+// metric.wrap(p) (:821-824): from_fractional(frac_wrap_to_unit_cell(to_fractional(p)))
+__host__ __device__ inline V3 periodic_wrap(const Periodic& P, const V3& p) {
+  V3 o = p;
+  if (P.on[0]) o.x = P.L[0] * safe_unit_mod1(P.inv[0] * p.x);
+  if (P.on[1]) o.y = P.L[1] * safe_unit_mod1(P.inv[1] * p.y);
+  if (P.on[2]) o.z = P.L[2] * safe_unit_mod1(P.inv[2] * p.z);
+  return o;
+}
+// unwrap_points_to_ref(point, metric, ref) (:1333-1339): ref + metric.sep(ref, point). Spheres and spherocylinders
+// unwrap their centre this way (:1487-1516).
+__host__ __device__ inline V3 periodic_unwrap(const Periodic& P, const V3& p, const V3& ref) {
+  return ref + periodic_sep(P, ref, p);
+}
+
 // distance(Point, Point, sep)  mundy/geom/src/mundy_geom/distance/PointPoint.hpp:54-62
 __host__ __device__ inline double dist_pp(const V3& p1, const V3& p2, V3& sep) {
   sep = p2 - p1;

@@ -311,6 +311,8 @@ extern "C" int mb200_collision_step_dist(mb200_neighbor_links* h, mb200_comm* co
   MB200_REQUIRE(g->n > 0 && g->n % comm->world == 0, "the number of bodies must be a positive multiple of the world size");
   MB200_REQUIRE(g->n < (int64_t(1) << 31) && g->center && g->radius, "bad global bodies");
   if (g->kind) MB200_REQUIRE(g->quat && g->length, "kind given without quat/length");
+  MB200_REQUIRE(!h->periodic.any, "a periodic box is not supported on the multi-GPU path yet (ghost selection is by "
+                                  "free-space bounding boxes)");
   MB200_TRY(require_device());
   const NcclApi* nccl = nccl_api();
   if (!nccl) return MB200_ERR_COMM;

@@ -10,7 +10,7 @@ namespace mb200 {
 // Caller layout -> 32-byte body records (shapes.cuh). perm == NULL: identity. b1 == NULL: spheres only.
 int pack_bodies(cudaStream_t st, const mb200_bodies* b, const int32_t* perm, D4* b0, D4* b1);
 int narrow_phase_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const D4* b0, const D4* b1,
-                         double* phi, double* normal, double* arm_i, double* arm_j);
+                         double* phi, double* normal, double* arm_i, double* arm_j, const Periodic& P);
 
 // lcp.cu ---------------------------------------------------------------------------------------------------------
 // Body-major incidence lists of a pair list: for body b, list[ptr[b] .. ptr[b+1]) holds 2*contact+side in ascending
@@ -54,7 +54,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
 // Narrow phase straight into contact records (the step's path).
 // perm (Morton -> caller index, nullable): pairs are evaluated with the lower caller index first.
 int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const uint32_t* perm, const D4* b0,
-                            const D4* b1, bool six, D4* rec);
+                            const D4* b1, bool six, D4* rec, const Periodic& P);
 // step.cu: the step after the link list is known (dist != NULL on the multi-GPU path)
 
 

@@ -6,6 +6,7 @@ struct mb200_neighbor_links {
   // builder parameters (GenNeighborLinkers.hpp:401-462)
   double buffer = 0.0;
   int filter = MB200_FILTER_NONE;
+  mb200::Periodic periodic = mb200::make_periodic(nullptr);  // orthorhombic periodic box (off by default)
   // state of the last build
   bool built = false;
   bool rods = false;

@@ -44,7 +44,7 @@ template <bool RODS, bool ARMS>
 __global__ void __launch_bounds__(kTile)
     narrow_phase_kernel(int64_t npairs, const int2* __restrict__ pairs, const D4* __restrict__ b0,
                         const D4* __restrict__ b1, double* __restrict__ phi, double* __restrict__ normal,
-                        double* __restrict__ arm_i, double* __restrict__ arm_j) {
+                        double* __restrict__ arm_i, double* __restrict__ arm_j, Periodic P) {
   __shared__ __align__(16) double s_n[3 * kTile];
   __shared__ __align__(16) double s_ai[ARMS ? 3 * kTile : 2];
   __shared__ __align__(16) double s_aj[ARMS ? 3 * kTile : 2];
@@ -55,7 +55,9 @@ __global__ void __launch_bounds__(kTile)
     const int t = threadIdx.x;
     if (t < cnt) {
       const int2 p = __ldg(pairs + base + t);
-      const D4 b0i = ldg256(b0 + p.x), b0j = ldg256(b0 + p.y);
+      const D4 b0i = ldg256(b0 + p.x);
+      D4 b0j = ldg256(b0 + p.y);
+      if (P.any) b0j = unwrap_to(P, b0i, b0j);  // periodic box: j unwrapped to i's centre
       D4 b1i{0, 0, 0, 0}, b1j{0, 0, 0, 0};
       if (RODS) {
         b1i = ldg256(b1 + p.x);
@@ -83,7 +85,7 @@ __global__ void __launch_bounds__(kTile)
 template <bool RODS, bool SIX>
 __global__ void __launch_bounds__(256)
     narrow_phase_rec_kernel(int64_t npairs, const int2* __restrict__ pairs, const uint32_t* __restrict__ perm,
-                            const D4* __restrict__ b0, const D4* __restrict__ b1, D4* __restrict__ rec) {
+                            const D4* __restrict__ b0, const D4* __restrict__ b1, D4* __restrict__ rec, Periodic P) {
   const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (c >= npairs) return;
   const int2 p = __ldg(pairs + c);
@@ -97,9 +99,9 @@ __global__ void __launch_bounds__(256)
   // whatever the Morton order of the two: results do not depend on the internal ordering or on the rank.
   PairGeom g;
   if (!perm || perm[p.x] < perm[p.y]) {
-    g = pair_geometry<RODS>(b0i, b1i, b0j, b1j);
+    g = pair_geometry<RODS>(b0i, b1i, P.any ? unwrap_to(P, b0i, b0j) : b0j, b1j);
   } else {
-    const PairGeom r = pair_geometry<RODS>(b0j, b1j, b0i, b1i);
+    const PairGeom r = pair_geometry<RODS>(b0j, b1j, P.any ? unwrap_to(P, b0j, b0i) : b0i, b1i);
     g.sep = r.sep;
     g.n = V3{-r.n.x, -r.n.y, -r.n.z};
     g.arm_i = r.arm_j;
@@ -118,14 +120,14 @@ __global__ void __launch_bounds__(256)
 }  // namespace
 
 int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const uint32_t* perm, const D4* b0,
-                            const D4* b1, bool six, D4* rec) {
+                            const D4* b1, bool six, D4* rec, const Periodic& P) {
   if (npairs == 0) return MB200_OK;
   const int grid = grid_for(npairs, 256);
   const int2* p2 = reinterpret_cast<const int2*>(pairs);
   if (b1 && six)
-    narrow_phase_rec_kernel<true, true><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, b1, rec);
+    narrow_phase_rec_kernel<true, true><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, b1, rec, P);
   else if (!b1 && !six)
-    narrow_phase_rec_kernel<false, false><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, nullptr, rec);
+    narrow_phase_rec_kernel<false, false><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, nullptr, rec, P);
   else {
     set_error("narrow_phase_to_records: rods and 6-DOF records go together");
     return MB200_ERR_INVALID_ARGUMENT;
@@ -135,21 +137,21 @@ int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pair
 }
 
 int narrow_phase_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const D4* b0, const D4* b1,
-                         double* phi, double* normal, double* arm_i, double* arm_j) {
+                         double* phi, double* normal, double* arm_i, double* arm_j, const Periodic& P) {
   if (npairs == 0) return MB200_OK;
   const int grid = grid_for(npairs, kTile, kSMs * 8);
   const int2* p2 = reinterpret_cast<const int2*>(pairs);
   const bool arms = arm_i && arm_j;
   if (b1) {
     if (arms)
-      narrow_phase_kernel<true, true><<<grid, kTile, 0, st>>>(npairs, p2, b0, b1, phi, normal, arm_i, arm_j);
+      narrow_phase_kernel<true, true><<<grid, kTile, 0, st>>>(npairs, p2, b0, b1, phi, normal, arm_i, arm_j, P);
     else
-      narrow_phase_kernel<true, false><<<grid, kTile, 0, st>>>(npairs, p2, b0, b1, phi, normal, nullptr, nullptr);
+      narrow_phase_kernel<true, false><<<grid, kTile, 0, st>>>(npairs, p2, b0, b1, phi, normal, nullptr, nullptr, P);
   } else {
     if (arms)
-      narrow_phase_kernel<false, true><<<grid, kTile, 0, st>>>(npairs, p2, b0, nullptr, phi, normal, arm_i, arm_j);
+      narrow_phase_kernel<false, true><<<grid, kTile, 0, st>>>(npairs, p2, b0, nullptr, phi, normal, arm_i, arm_j, P);
     else
-      narrow_phase_kernel<false, false><<<grid, kTile, 0, st>>>(npairs, p2, b0, nullptr, phi, normal, nullptr, nullptr);
+      narrow_phase_kernel<false, false><<<grid, kTile, 0, st>>>(npairs, p2, b0, nullptr, phi, normal, nullptr, nullptr, P);
   }
   MB200_LAUNCHED();
   return MB200_OK;
@@ -159,8 +161,9 @@ int narrow_phase_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, 
 
 using namespace mb200;
 
-extern "C" int mb200_narrow_phase(mb200_stream stream, const mb200_bodies* bodies, int64_t npairs, const int32_t* pairs,
-                                  double* phi, double* normal, double* arm_i, double* arm_j) {
+extern "C" int mb200_narrow_phase_periodic(mb200_stream stream, const mb200_bodies* bodies, int64_t npairs,
+                                           const int32_t* pairs, const double* cell_size_h, double* phi,
+                                           double* normal, double* arm_i, double* arm_j) {
   MB200_REQUIRE(bodies && bodies->n >= 0 && npairs >= 0, "bad sizes");
   if (npairs == 0) return MB200_OK;
   MB200_REQUIRE(bodies->center && bodies->radius && pairs && phi && normal, "null pointer");
@@ -173,5 +176,11 @@ extern "C" int mb200_narrow_phase(mb200_stream stream, const mb200_bodies* bodie
   MB200_TRY(b0.alloc(bodies->n, st));
   if (rods) MB200_TRY(b1.alloc(bodies->n, st));
   MB200_TRY(pack_bodies(st, bodies, nullptr, b0.p, rods ? b1.p : nullptr));
-  return narrow_phase_records(st, npairs, pairs, b0.p, rods ? b1.p : nullptr, phi, normal, arm_i, arm_j);
+  return narrow_phase_records(st, npairs, pairs, b0.p, rods ? b1.p : nullptr, phi, normal, arm_i, arm_j,
+                              make_periodic(cell_size_h));
+}
+
+extern "C" int mb200_narrow_phase(mb200_stream stream, const mb200_bodies* bodies, int64_t npairs, const int32_t* pairs,
+                                  double* phi, double* normal, double* arm_i, double* arm_j) {
+  return mb200_narrow_phase_periodic(stream, bodies, npairs, pairs, nullptr, phi, normal, arm_i, arm_j);
 }

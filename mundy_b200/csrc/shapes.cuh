@@ -68,4 +68,18 @@ __device__ inline bool is_candidate(const D4& si, const D4& sj) {
   return d2 <= s * s;
 }
 
+// Periodic forms: the second body is unwrapped to the first body's reference point (its centre,
+// periodicity.hpp:925-933 reference_point) with unwrap_points_to_ref (:1487-1516) and the free-space functions above
+// are applied to the result; the search predicate measures the centre separation with metric.sep (:814-818).
+__device__ inline D4 unwrap_to(const Periodic& P, const D4& b0i, const D4& b0j) {
+  const V3 c = periodic_unwrap(P, V3{b0j.x, b0j.y, b0j.z}, V3{b0i.x, b0i.y, b0i.z});
+  return D4{c.x, c.y, c.z, b0j.w};
+}
+__device__ inline bool is_candidate_periodic(const Periodic& P, const D4& si, const D4& sj) {
+  const V3 d = periodic_sep(P, V3{si.x, si.y, si.z}, V3{sj.x, sj.y, sj.z});
+  const double d2 = d.x * d.x + (d.y * d.y + d.z * d.z);
+  const double s = si.w + sj.w;
+  return d2 <= s * s;
+}
+
 }  // namespace mb200

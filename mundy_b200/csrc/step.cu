@@ -3,6 +3,7 @@
 //   generate links if needed -> narrow phase -> phi0 += dt D^T U_ext -> BBPGD -> U = U_ext + U_col -> Euler.
 // The step works on bodies gathered into Morton order (the order of the link list) and scatters results back to the
 // caller's order at the end.
+#include <cmath>
 #include <vector>
 
 #include "links.cuh"
@@ -117,6 +118,17 @@ int mb200_neighbor_links_set_search_filter(mb200_neighbor_links* h, int filter) 
   return MB200_OK;
 }
 
+int mb200_neighbor_links_set_periodic(mb200_neighbor_links* h, const double* cell_size_h) {
+  MB200_REQUIRE(h, "null handle");
+  const Periodic P = make_periodic(cell_size_h);
+  for (int d = 0; d < 3; ++d) {
+    MB200_REQUIRE(!cell_size_h || std::isfinite(cell_size_h[d]), "non-finite cell size");
+    if (P.on[d] != h->periodic.on[d] || P.L[d] != h->periodic.L[d]) h->built = false;
+  }
+  h->periodic = P;
+  return MB200_OK;
+}
+
 int mb200_neighbor_links_generate(mb200_neighbor_links* h, mb200_stream stream, const mb200_bodies* bodies, int force,
                                   int* rebuilt_h) {
   MB200_REQUIRE(h, "null handle");
@@ -139,8 +151,8 @@ int mb200_neighbor_links_get_pairs(mb200_neighbor_links* h, mb200_stream stream,
   return canonical_pairs(st, h, pairs_out);
 }
 
-int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, const double* search_radius,
-                       int32_t* pairs_out, int64_t capacity, int64_t* count_h) {
+int mb200_search_pairs_periodic(mb200_stream stream, int64_t n, const double* center, const double* search_radius,
+                                const double* cell_size_h, int32_t* pairs_out, int64_t capacity, int64_t* count_h) {
   MB200_REQUIRE(n >= 0 && n < (int64_t(1) << 31) && count_h, "bad arguments");
   *count_h = 0;
   if (n == 0) return MB200_OK;
@@ -148,6 +160,7 @@ int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, con
   MB200_TRY(require_device());
   cudaStream_t st = as_stream(stream);
   mb200_neighbor_links tmp;
+  tmp.periodic = make_periodic(cell_size_h);
   mb200_bodies b{n, const_cast<double*>(center), nullptr, search_radius, nullptr, nullptr};
   MB200_TRY(build_links(st, &tmp, &b, search_radius, nullptr));
   *count_h = tmp.npairs;
@@ -161,6 +174,11 @@ int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, con
   }
   MB200_CUDA(cudaStreamSynchronize(st));  // tmp's buffers are freed when it goes out of scope
   return MB200_OK;
+}
+
+int mb200_search_pairs(mb200_stream stream, int64_t n, const double* center, const double* search_radius,
+                       int32_t* pairs_out, int64_t capacity, int64_t* count_h) {
+  return mb200_search_pairs_periodic(stream, n, center, search_radius, nullptr, pairs_out, capacity, count_h);
 }
 
 }  // extern "C"
@@ -206,7 +224,8 @@ int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodi
     }
     {  // narrow phase on the links
       StageScope ps(MB200_STAGE_NARROW, st);
-      MB200_TRY(narrow_phase_to_records(st, C, h->pairs.p, h->perm.p, h->b0.p, rods ? h->b1.p : nullptr, rods, h->rec.p));
+      MB200_TRY(narrow_phase_to_records(st, C, h->pairs.p, h->perm.p, h->b0.p, rods ? h->b1.p : nullptr, rods, h->rec.p,
+                                        h->periodic));
     }
     // LCP
     MB200_TRY(h->vec_c.reserve(3 * n));

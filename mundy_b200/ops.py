@@ -32,6 +32,13 @@ def _i32(t):
     return _p(t)
 
 
+def _cell(cell_size):
+    """Host double[3] of the periodic cell edges (entry <= 0: free axis); None -> NULL (free space)."""
+    if cell_size is None:
+        return None
+    return (C.c_double * 3)(*[float(x) for x in cell_size])
+
+
 def _new(n, like, dtype=torch.float64):
     return torch.empty(n, dtype=dtype, device=like.device)
 
@@ -100,28 +107,57 @@ def make_bodies(center, radius, quat=None, length=None, kind=None):
     return b
 
 
-def narrow_phase(bodies, pairs, arms=False):
+def periodic_sep(cell_size, p1, p2):
+    out = torch.empty_like(p1)
+    check(lib.mb200_periodic_sep(_stream(), p1.shape[0], _cell(cell_size), _f64(p1), _f64(p2), _f64(out)),
+          "periodic_sep")
+    return out
+
+
+def periodic_wrap(cell_size, p):
+    out = torch.empty_like(p)
+    check(lib.mb200_periodic_wrap(_stream(), p.shape[0], _cell(cell_size), _f64(p), _f64(out)), "periodic_wrap")
+    return out
+
+
+def periodic_unwrap_points(cell_size, p, ref):
+    out = torch.empty_like(p)
+    check(lib.mb200_periodic_unwrap_points(_stream(), p.shape[0], _cell(cell_size), _f64(p), _f64(ref), _f64(out)),
+          "periodic_unwrap_points")
+    return out
+
+
+def periodic_unwrap_segments(cell_size, start, end, ref):
+    o0, o1 = torch.empty_like(start), torch.empty_like(end)
+    check(lib.mb200_periodic_unwrap_segments(_stream(), start.shape[0], _cell(cell_size), _f64(start), _f64(end),
+                                             _f64(ref), _f64(o0), _f64(o1)), "periodic_unwrap_segments")
+    return o0, o1
+
+
+def narrow_phase(bodies, pairs, arms=False, cell_size=None):
     npairs = pairs.shape[0]
     ref = bodies._keep[0]
     phi, normal = _new(npairs, ref), _new((npairs, 3), ref)
     ai = _new((npairs, 3), ref) if arms else None
     aj = _new((npairs, 3), ref) if arms else None
-    check(lib.mb200_narrow_phase(_stream(), C.byref(bodies), npairs, _i32(pairs), _f64(phi), _f64(normal), _f64(ai),
-                                 _f64(aj)), "narrow_phase")
+    check(lib.mb200_narrow_phase_periodic(_stream(), C.byref(bodies), npairs, _i32(pairs), _cell(cell_size), _f64(phi),
+                                          _f64(normal), _f64(ai), _f64(aj)), "narrow_phase")
     return phi, normal, ai, aj
 
 
-def search_pairs(center, search_radius, capacity=None):
+def search_pairs(center, search_radius, capacity=None, cell_size=None):
     n = search_radius.numel()
     count = C.c_int64(0)
     if capacity is None:
         capacity = max(64 * n, 1024)
     out = torch.empty((capacity, 2), dtype=torch.int32, device=center.device)
-    st = lib.mb200_search_pairs(_stream(), n, _f64(center), _f64(search_radius), _i32(out), capacity, C.byref(count))
+    cell = _cell(cell_size)
+    st = lib.mb200_search_pairs_periodic(_stream(), n, _f64(center), _f64(search_radius), cell, _i32(out), capacity,
+                                         C.byref(count))
     if st == -3:  # capacity: retry with the exact size
         out = torch.empty((count.value, 2), dtype=torch.int32, device=center.device)
-        st = lib.mb200_search_pairs(_stream(), n, _f64(center), _f64(search_radius), _i32(out), count.value,
-                                    C.byref(count))
+        st = lib.mb200_search_pairs_periodic(_stream(), n, _f64(center), _f64(search_radius), cell, _i32(out),
+                                             count.value, C.byref(count))
     check(st, "search_pairs")
     return out[: count.value]
 
@@ -147,6 +183,11 @@ class NeighborLinks:
 
     def set_search_filter(self, filt):
         check(lib.mb200_neighbor_links_set_search_filter(self._h, int(filt)), "set_search_filter")
+        return self
+
+    def set_periodic(self, cell_size):
+        """Orthorhombic periodic box (cell edge per axis, <= 0: free axis); None switches it off."""
+        check(lib.mb200_neighbor_links_set_periodic(self._h, _cell(cell_size)), "set_periodic")
         return self
 
     def generate(self, bodies, force=False):

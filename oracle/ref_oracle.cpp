@@ -9,12 +9,15 @@
 //   geom::compute_aabb          mundy/geom/src/mundy_geom/compute_aabb.hpp:47-143
 //   geom::distance(...)         mundy/geom/src/mundy_geom/distance/{PointPoint,PointLineSegment,LineSegmentLineSegment,
 //                                                                    SphereSphere,LineSegmentSphere}.hpp
+//   geom::PeriodicScaledMetric / PeriodicMetricX,Y,XY,YZ, unwrap_points_to_ref
+//                               mundy/geom/src/mundy_geom/periodicity.hpp:335-845,1333-1516
 //   math::rotate_quaternion     mundy/math/src/mundy_math/Quaternion.hpp:1359-1385
 //   math::solve_cqpp/solve_lcp  mundy/math/src/mundy_math/convex.hpp:789-845 (KokkosBackend + MundyMathBackend)
 #include <Kokkos_Core.hpp>
 
 #include <mundy_geom/compute_aabb.hpp>
 #include <mundy_geom/distance.hpp>
+#include <mundy_geom/periodicity.hpp>
 #include <mundy_geom/primitives.hpp>
 #include <mundy_math/Quaternion.hpp>
 #include <mundy_math/Vector3.hpp>
@@ -135,6 +138,48 @@ void ref_seg_sphere(long n, const double* p1, const double* p2, const double* c,
     t[i] = tt;
     put3(cp + 3 * i, cpt);
     put3(sep + 3 * i, sp);
+  }
+}
+
+// ---- periodic metrics (periodicity.hpp). mode = bit mask of the periodic axes: 7 = PeriodicScaledMetric (:743-845),
+// 1 = PeriodicMetricX, 2 = PeriodicMetricY, 3 = PeriodicMetricXY, 6 = PeriodicMetricYZ (:335-741).
+// op: 0 sep(a,b) | 1 wrap(a) | 2 unwrap_points_to_ref(Point a, m, ref b) | 3 unwrap_points_to_ref(LineSegment(a,c), m, ref b)
+//     4 centre of unwrap_points_to_ref(Sphere(a, 1), m, b) | 5 centre of unwrap_points_to_ref(Spherocylinder(a,..), m, b)
+}  // extern "C"
+template <class Metric>
+static void periodic_apply(const Metric& m, int op, long n, const double* a, const double* b, const double* c,
+                           double* o0, double* o1) {
+  for (long i = 0; i < n; ++i) {
+    const P3 pa = pt(a + 3 * i);
+    if (op == 0) {
+      put3(o0 + 3 * i, m.sep(pa, pt(b + 3 * i)));
+    } else if (op == 1) {
+      put3(o0 + 3 * i, m.wrap(pa));
+    } else if (op == 2) {
+      put3(o0 + 3 * i, mg::unwrap_points_to_ref(pa, m, pt(b + 3 * i)));
+    } else if (op == 3) {
+      const auto seg = mg::unwrap_points_to_ref(mg::LineSegment<double>(pa, pt(c + 3 * i)), m, pt(b + 3 * i));
+      put3(o0 + 3 * i, seg.start());
+      put3(o1 + 3 * i, seg.end());
+    } else if (op == 4) {
+      put3(o0 + 3 * i, mg::unwrap_points_to_ref(mg::Sphere<double>(pa, 1.0), m, pt(b + 3 * i)).center());
+    } else {
+      const mg::Spherocylinder<double> sc(pa, Quat(1.0, 0.0, 0.0, 0.0), 0.5, 2.0);
+      put3(o0 + 3 * i, mg::unwrap_points_to_ref(sc, m, pt(b + 3 * i)).center());
+    }
+  }
+}
+
+extern "C" {
+int ref_periodic(int mode, int op, long n, const double* cell, const double* a, const double* b, const double* c,
+                 double* o0, double* o1) {
+  switch (mode) {
+    case 7: periodic_apply(mg::PeriodicScaledMetric<double>(V3(cell[0], cell[1], cell[2])), op, n, a, b, c, o0, o1); return 0;
+    case 1: periodic_apply(mg::PeriodicMetricX<double>(cell[0]), op, n, a, b, c, o0, o1); return 0;
+    case 2: periodic_apply(mg::PeriodicMetricY<double>(cell[1]), op, n, a, b, c, o0, o1); return 0;
+    case 3: periodic_apply(mg::PeriodicMetricXY<double>(cell[0], cell[1]), op, n, a, b, c, o0, o1); return 0;
+    case 6: periodic_apply(mg::PeriodicMetricYZ<double>(cell[1], cell[2]), op, n, a, b, c, o0, o1); return 0;
+    default: return -1;
   }
 }
 

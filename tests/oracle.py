@@ -145,43 +145,76 @@ def search_radii(r, buffer, kind=None, length=None):
     return S
 
 
-def search(pos, S, brute=False):
+def _cell(cell):
+    return None if cell is None else np.ascontiguousarray(cell, dtype=_d)
+
+
+PERIODIC_MODES = {7: "PeriodicScaledMetric", 1: "PeriodicMetricX", 2: "PeriodicMetricY", 3: "PeriodicMetricXY",
+                  6: "PeriodicMetricYZ"}
+
+
+def periodic(op, cell, a, b=None, c=None, lib=None):
+    """Periodic leaves. op: 0 sep(a,b) | 1 wrap(a) | 2 unwrap point a to ref b | 3 unwrap segment (a,c) to ref b
+    (| 4, 5: centre of the unwrapped Sphere / Spherocylinder, reference library only).
+    lib=None: the oracle restatement; lib=ref: the reference's own classes (mode = mask of the axes with cell > 0)."""
+    cell = _cell(cell)
+    a, b, c = _a(a), _a(b), _a(c)
+    o0 = np.empty_like(a)
+    o1 = np.empty_like(a) if op == 3 else None
+    if lib is None:
+        fn = orc.orc_periodic
+        fn.restype = None
+        fn(C.c_int(op), C.c_long(len(a)), _p(cell), _p(a), _p(b), _p(c), _p(o0), _p(o1))
+    else:
+        mode = sum(1 << d for d in range(3) if cell[d] > 0)
+        fn = lib.ref_periodic
+        fn.restype = C.c_int
+        st = fn(C.c_int(mode), C.c_int(op), C.c_long(len(a)), _p(cell), _p(a), _p(b), _p(c), _p(o0), _p(o1))
+        assert st == 0, f"no reference metric for periodic axes mask {mode}"
+    return (o0, o1) if op == 3 else o0
+
+
+def search(pos, S, brute=False, cell=None):
     pos, S = _a(pos), _a(S)
     n = len(S)
-    fn = "orc_search_brute" if brute else "orc_search_cells"
+    fn = "orc_search_brute_periodic" if brute else "orc_search_cells_periodic"
+    cell = _cell(cell)
     cap = max(1024, 64 * n)
     while True:
         pairs = np.empty((cap, 2), dtype=_i)
-        cnt = _call(orc, fn, n, pos, S, pairs, cap, restype=C.c_long)
+        cnt = _call(orc, fn, n, pos, S, cell, pairs, cap, restype=C.c_long)
         if cnt <= cap:
             return pairs[:cnt].copy()
         cap = cnt
 
 
-def filter_shape_distance(pairs, pos, quat, r, length, kind, cutoff):
+def filter_shape_distance(pairs, pos, quat, r, length, kind, cutoff, cell=None):
     pairs = _a(pairs, _i)
     out = np.empty_like(pairs)
-    cnt = _call(orc, "orc_filter_shape_distance", len(pairs), pairs, _a(pos), _a(quat), _a(r), _a(length),
-                _a(kind, _i), float(cutoff), out, restype=C.c_long)
+    cnt = _call(orc, "orc_filter_shape_distance_periodic", len(pairs), pairs, _a(pos), _a(quat), _a(r), _a(length),
+                _a(kind, _i), float(cutoff), _cell(cell), out, restype=C.c_long)
     return out[:cnt].copy()
 
 
-def moved_too_much(pos, pos_at_build, buffer):
-    return bool(_call(orc, "orc_moved_too_much", len(pos), _a(pos), _a(pos_at_build), float(buffer), restype=C.c_int))
+def moved_too_much(pos, pos_at_build, buffer, cell=None):
+    return bool(_call(orc, "orc_moved_too_much_periodic", len(pos), _a(pos), _a(pos_at_build), float(buffer),
+                      _cell(cell), restype=C.c_int))
 
 
-def moved_too_much_shapes(pos, quat, length, kind, pos_at_build, quat_at_build, buffer):
-    return bool(_call(orc, "orc_moved_too_much_shapes", len(pos), _a(pos), _a(quat), _a(length), _a(kind, _i),
-                      _a(pos_at_build), _a(quat_at_build), float(buffer), restype=C.c_int))
+def moved_too_much_shapes(pos, quat, length, kind, pos_at_build, quat_at_build, buffer, cell=None):
+    return bool(_call(orc, "orc_moved_too_much_shapes_periodic", len(pos), _a(pos), _a(quat), _a(length),
+                      _a(kind, _i), _a(pos_at_build), _a(quat_at_build), float(buffer), _cell(cell),
+                      restype=C.c_int))
 
 
-def narrow_phase(pairs, pos, r, quat=None, length=None, kind=None, arms=False):
+def narrow_phase(pairs, pos, r, quat=None, length=None, kind=None, arms=False, cell=None):
     pairs = _a(pairs, _i)
     m = len(pairs)
     phi, normal = np.empty(m), np.empty((m, 3))
     ai = np.empty((m, 3)) if arms else None
     aj = np.empty((m, 3)) if arms else None
-    _call(orc, "orc_narrow_phase", m, pairs, _a(pos), _a(quat), _a(r), _a(length), _a(kind, _i), phi, normal, ai, aj)
+    _call(orc, "orc_narrow_phase_periodic", m, pairs, _a(pos), _a(quat), _a(r), _a(length), _a(kind, _i), _cell(cell),
+          phi, normal, ai, aj)
     return phi, normal, ai, aj
 
 
@@ -251,26 +284,26 @@ def abc_flow_force(pos):
 
 # ---- whole step (composition of the pieces above; the loop body of
 # scrap/parameter_interface/NGPSpheresLCP.cpp:1135-1292) ---------------------------------------------------------
-def collision_step(state, w, links, buffer, filt, mu, dt, tol, max_it, fixed, F_ext):
+def collision_step(state, w, links, buffer, filt, mu, dt, tol, max_it, fixed, F_ext, cell=None):
     """One collision step composed from the oracle pieces; `links` carries (pairs, ref_center) between steps."""
     c, q = state
     kind, L, r = w.get("kind"), w.get("length"), w["radius"]
     if links is not None:  # rebuild trigger of GenNeighborLinks::generate (GenNeighborLinkers.hpp:603-615)
         if filt and kind is not None:
-            if moved_too_much_shapes(c, q, L, kind, links[1], links[2], buffer):
+            if moved_too_much_shapes(c, q, L, kind, links[1], links[2], buffer, cell):
                 links = None
-        elif moved_too_much(c, links[1], buffer):
+        elif moved_too_much(c, links[1], buffer, cell):
             links = None
     rebuilt = links is None
     if links is None:
         S = search_radii(r, buffer, kind, L)
-        pairs = search(c, S)
+        pairs = search(c, S, cell=cell)
         if filt and kind is not None:
-            pairs = filter_shape_distance(pairs, c, q, r, L, kind, 2 * buffer)
+            pairs = filter_shape_distance(pairs, c, q, r, L, kind, 2 * buffer, cell)
         links = (pairs, c.copy(), None if q is None else q.copy())
     pairs = links[0]
     arms = kind is not None
-    phi, nrm, ai, aj = narrow_phase(pairs, c, r, q, L, kind, arms)
+    phi, nrm, ai, aj = narrow_phase(pairs, c, r, q, L, kind, arms, cell)
     Uext = Wext = None
     if F_ext is not None:
         Uext, Wext = apply_M(r, mu, F_ext, np.zeros_like(F_ext) if arms else None, q, kind)

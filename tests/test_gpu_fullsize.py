@@ -120,3 +120,33 @@ def test_cfg2_million_polydisperse_spheres(cuda):
     assert np.max(np.abs(F.sum(axis=0))) <= 1e-9 * np.abs(F).sum()
     phi1 = oracle.narrow_phase(pairs, host(c), w["radius"])[0]
     assert phi1.min() > -20 * tol
+
+
+def test_cfg2_million_polydisperse_spheres_periodic(cuda):
+    """cfg2 as BASELINE.json words it ("10^6 polydisperse spheres in a periodic box"): the whole link set equals the
+    oracle's periodic cell-list search (OpenMP, seconds at this size), links across the boundary exist, the solver
+    converges, forces balance, and after the step no nearest-image pair overlaps by more than the tolerance allows."""
+    from mundy_b200 import ops
+    w = wl.polydisperse_spheres(N, phi=0.35)
+    cell = [w["edge"]] * 3
+    mu, dt, tol, buffer = 1e-3, 1e-4, 1e-3, 0.25
+    c = dev(w["center"])
+    b = ops.make_bodies(c, dev(w["radius"]))
+    links = ops.NeighborLinks().set_search_buffer(buffer).set_periodic(cell)
+    Fcol = torch.empty((N, 3), dtype=torch.float64, device="cuda")
+    c0 = w["center"].copy()
+    st = links.step(b, mu, dt, tol, 10000, F_col=Fcol)
+    pairs = host(links.pairs())
+    S = w["radius"] + buffer
+    want = oracle.search(c0, S, cell=cell)
+    assert st.lcp.converged and st.num_links == len(pairs)
+    assert np.array_equal(pairs, want)
+    free = oracle.search(c0, S)
+    assert len(pairs) > len(free)  # the periodic images add links
+    phi0, nrm, _, _ = oracle.narrow_phase(pairs, c0, w["radius"], cell=cell)
+    across = np.abs(c0[pairs[:, 1]] - c0[pairs[:, 0]]).max(axis=1) > 0.5 * w["edge"]
+    assert across.sum() == len(pairs) - len(free) and phi0[across].max() <= 2 * buffer
+    F = host(Fcol)
+    assert np.max(np.abs(F.sum(axis=0))) <= 1e-9 * np.abs(F).sum()
+    phi1 = oracle.narrow_phase(pairs, host(c), w["radius"], cell=cell)[0]
+    assert phi1.min() > -20 * tol
