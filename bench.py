@@ -58,19 +58,27 @@ def parse_args():
 
 # ---- clocks ---------------------------------------------------------------------------------------------------------
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+    # Started BEFORE the warm-up steps (NVML start-up stalls the driver for tens of ms and would otherwise land inside the
+    # timed region); only samples stamped after mark() are used.
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
+        self.t0 = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms",
-                                       "200", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "50", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             pass
 
+    def mark(self):
+        import datetime
+        self.t0 = datetime.datetime.now()
+
     def stop(self):
+        import datetime
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         if self.p is None:
             return out
@@ -85,13 +93,15 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.f.read().splitlines():
             c = [x.strip() for x in line.split(",")]
-            if len(c) < 7:
+            if len(c) < 8:
                 continue
             try:
-                sm.append(float(c[0])), smax.append(float(c[1])), power.append(float(c[2]))
+                if self.t0 is not None and datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f") < self.t0:
+                    continue
+                sm.append(float(c[1])), smax.append(float(c[2])), power.append(float(c[3]))
             except ValueError:
                 continue
-            for name, v in zip(names, c[3:7]):
+            for name, v in zip(names, c[4:8]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         self.f.close()
@@ -234,6 +244,7 @@ def run_b200(args):
 
     for _ in range(args.prep):
         step()
+    sampler = ClockSampler(local) if rank == 0 else None
     for _ in range(args.warmup):
         step()
     log.clear()
@@ -241,16 +252,21 @@ def run_b200(args):
     # ---- timed region: device-resident -----------------------------------------------------------------------------
     if not args.no_stage_timers:
         ops.profile_enable(True)
-    sampler = ClockSampler(local) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = ops.kernel_launch_count()
     barrier()
+    if sampler:
+        sampler.mark()
     ev0.record()
+    marks = [ev0]
     for _ in range(args.steps):
         step()
+        marks.append(torch.cuda.Event(enable_timing=True))
+        marks[-1].record()
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
+    ms_steps = [round(marks[k].elapsed_time(marks[k + 1]), 3) for k in range(args.steps)]
     launches = ops.kernel_launch_count() - launches0
     clocks = sampler.stop() if sampler else None
     stages = ops.profile_read() if not args.no_stage_timers else {}
@@ -382,7 +398,7 @@ def run_b200(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": workload_config(args, n),
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-        "lcp_iters_per_step": [x[0] for x in tlog], "links_per_step": int(C), "rebuilds": sum(x[2] for x in tlog),
+        "lcp_iters_per_step": [x[0] for x in tlog], "ms_steps": ms_steps, "links_per_step": int(C), "rebuilds": sum(x[2] for x in tlog),
         "all_converged": all(x[3] for x in tlog), "stages": stage_out, "prep_steps": args.prep,
     }
     if comm is not None:
