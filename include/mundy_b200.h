@@ -333,7 +333,8 @@ int mb200_collision_step_host(mb200_neighbor_links* links, mb200_stream stream, 
  * [r n/W, (r+1) n/W). A rank works on its owned bodies plus the foreign bodies within search reach (ghosts). A link
  * with one owned end is kept by both owners and its gamma is computed redundantly (bit-identically) on both; it is
  * counted in the global sums by the owner of its lower-index body (scrap/UnitTestMundy.cpp:553-555). Per solver
- * iteration the owners' velocity records go to the ghost rows (NCCL send/recv) and the four scalars are all-gathered;
+ * iteration the owners' velocity records go to the ghost rows and the ranks' four scalars to every rank: through peer
+ * memory from inside the kernels (default) or with NCCL send/recv + all-gather (see mb200_comm_exchange_mode);
  * per step the advanced owned state is all-gathered into every replica.
  * ------------------------------------------------------------------------------------------------------------- */
 typedef struct mb200_comm mb200_comm;
@@ -345,6 +346,12 @@ int mb200_comm_create(mb200_comm** out, int world, int rank, const char* id_h);
 int mb200_comm_destroy(mb200_comm* comm);
 int mb200_comm_world(const mb200_comm* comm);
 int mb200_comm_rank(const mb200_comm* comm);
+
+/* How the solver's per-iteration exchange runs: 1 = peer memory (CUDA IPC mappings over NVLink: the body / contact kernels
+ * store velocity records and reduction totals straight into the peers' memory and signal with system-scope flags; chosen
+ * automatically at the first distributed build when every rank could map every other rank), 0 = NCCL send/recv +
+ * all-gather (fallback; forced with the environment variable MB200_DIST_EXCHANGE=nccl). Valid after the first step. */
+int mb200_comm_exchange_mode(const mb200_comm* comm);
 
 /* One collision timestep on the replicated global body set (device arrays of ALL n bodies on every rank; n must be a
  * multiple of the world size). On return every replica holds the advanced centres / quaternions of all bodies.

@@ -122,6 +122,7 @@ SIGNATURES = {
     "mb200_comm_destroy": (C.c_int, [vp]),
     "mb200_comm_world": (C.c_int, [vp]),
     "mb200_comm_rank": (C.c_int, [vp]),
+    "mb200_comm_exchange_mode": (C.c_int, [vp]),
     "mb200_collision_step_dist": (C.c_int, [vp, vp, vp, P(Bodies), P(StepParams), vp, vp, vp, vp, P(StepStats)]),
     "mb200_dist_local_counts": (C.c_int, [vp, P(c_i64), P(c_i64)]),
     "mb200_collision_step_host": (C.c_int, [vp, vp, P(Bodies), P(StepParams), vp, vp, vp, vp, vp, vp, P(StepStats)]),

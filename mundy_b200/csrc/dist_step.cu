@@ -295,6 +295,20 @@ int dist_build(cudaStream_t st, mb200_neighbor_links* h, mb200_comm* comm, const
   // owned bodies are never flagged for receiving, so the compacted receive order is peer-block order
   compact_halo_kernel<<<grid_for(nl, 256), 256, 0, st>>>(nl, nl, 0, recvflag.p, rpos.p, D.inv_perm.p, D.recv_idx.p);
   MB200_LAUNCHED();
+  // 8. peer-memory exchange: map the ranks' velocity arenas once (any local set fits in 2 records per global body), then
+  //    tell every peer in which rows of MY arena its records belong: my receive list, in the order of its send list
+  MB200_TRY(peer_setup(comm, st, 2 * N));
+  if (comm->peer.ok) {
+    const NcclApi* nccl = nccl_api();
+    MB200_TRY(D.remote_row.reserve(ns + 1));
+    MB200_NCCL(nccl->GroupStart());
+    for (int q = 0; q < D.npeers; ++q) {
+      const int64_t cs = D.send_off[q + 1] - D.send_off[q], cr = D.recv_off[q + 1] - D.recv_off[q];
+      if (cr > 0) MB200_NCCL(nccl->Send(D.recv_idx.p + D.recv_off[q], cr, ncclUint32, D.peer[q], comm->comm, st));
+      if (cs > 0) MB200_NCCL(nccl->Recv(D.remote_row.p + D.send_off[q], cs, ncclUint32, D.peer[q], comm->comm, st));
+    }
+    MB200_NCCL(nccl->GroupEnd());
+  }
   D.built = true;
   return MB200_OK;
 }
@@ -371,6 +385,11 @@ extern "C" int mb200_collision_step_dist(mb200_neighbor_links* h, mb200_comm* co
   for (int q = 0; q < 17; ++q) ds.send_off[q] = D.send_off[q], ds.recv_off[q] = D.recv_off[q];
   ds.send_idx = D.send_idx.p, ds.recv_idx = D.recv_idx.p, ds.sendbuf = D.sendbuf.p, ds.recvbuf = D.recvbuf.p;
   ds.red = D.red.p;
+  const bool peer_mode = comm->peer.ok;
+  ds.peer_dev = peer_mode ? comm->peer.dev : nullptr;
+  ds.vel_arena = peer_mode ? comm->peer.vel : nullptr;
+  ds.remote_row = peer_mode ? D.remote_row.p : nullptr;
+  ds.halo_seq = &comm->peer.halo_seq, ds.red_seq = &comm->peer.red_seq;
   mb200_step_params p = *params;
   p.throw_on_max_iters = 0;  // reported through stats (every rank must finish the collective sequence)
   MB200_TRY(step_core(h, st, &lb, &p, F_ext ? D.fext.p : nullptr, T_ext ? D.text.p : nullptr, F_col ? D.fcol.p : nullptr,
@@ -406,3 +425,5 @@ extern "C" int mb200_dist_local_counts(const mb200_neighbor_links* h, int64_t* n
   *n_ghost_rows_h = h->dist.built ? h->dist.recv_off[h->dist.npeers] : 0;
   return MB200_OK;
 }
+
+extern "C" int mb200_comm_exchange_mode(const mb200_comm* comm) { return (comm && comm->peer.ok) ? 1 : 0; }

@@ -46,6 +46,12 @@ struct DistSolve {
   D4* sendbuf;                 // 2 records per body capacity
   D4* recvbuf;
   double* red;                 // device scratch: [4] local totals followed by [4 * world] gathered
+  // peer-memory exchange (comm.cuh; peer_dev == NULL: the NCCL calls above are used)
+  const struct PeerDev* peer_dev;      // device table of every rank's mapped control block and velocity arena
+  D4* vel_arena;                       // this rank's velocity arena (the solver's velocity records live here)
+  const uint32_t* remote_row;          // [send list] row of the body in the destination rank's arena
+  unsigned long long* halo_seq;        // host counters kept in the communicator (monotone across solves)
+  unsigned long long* red_seq;
 };
 int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& inc, const mb200_lcp_params* params,
                     const double* U_ext, const double* W_ext, const double* gamma0, double* gamma_out,

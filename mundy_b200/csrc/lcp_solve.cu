@@ -35,6 +35,8 @@ struct LcpState {
   int32_t done;
   int32_t converged;
   uint32_t ticket;
+  uint32_t ticket2;  // halo_push_kernel's CTA counter
+  int32_t error;     // multi-GPU: a peer did not answer in time
 };
 
 struct LcpArgs {  // everything the iteration kernels need; passed by value
@@ -53,7 +55,42 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
   // multi-GPU (null on one GPU): contacts this rank adds to the global sums; where the last CTA leaves the local totals
   const uint8_t* counted;
   double* red_local;
+  // peer-memory exchange (null: NCCL): table of the ranks' mapped addresses; sequence numbers of the velocity halo this
+  // rate pass consumes and of the reduction it produces
+  const PeerDev* peer;
+  unsigned long long halo_seq, red_seq;
 };
+
+// ---- system-scope signalling between GPUs -----------------------------------------------------------------------
+__device__ inline void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ inline unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ inline double ld_relaxed_sys(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ inline unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+constexpr unsigned long long kPeerTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;
+// Spin until *flag >= want (a peer's release store). false after kPeerTimeoutNs: the caller raises state->error.
+__device__ inline bool wait_flag(const unsigned long long* flag, unsigned long long want) {
+  if (ld_acquire_sys(flag) >= want) return true;
+  const unsigned long long t0 = global_ns();
+  for (;;) {
+    if (ld_acquire_sys(flag) >= want) return true;
+    if (global_ns() - t0 > kPeerTimeoutNs) return false;
+    __nanosleep(64);
+  }
+}
 
 __device__ inline double2 ldg128(const double2* p) {
   double2 r;
@@ -384,7 +421,46 @@ __global__ void __launch_bounds__(256) halo_unpack_kernel(int64_t count, int rec
   vel[b * recs + (k % recs)] = buf[k];
 }
 
+// Peer-memory velocity halo: the owners' records are stored straight into the ghost rows of the peers' velocity arenas
+// over NVLink (no staging buffer, no NCCL call); the last CTA to finish publishes the sequence number to every rank
+// with a system-scope release store. The consumer is the peers' rate_pass_kernel.
+struct PushArgs {
+  int npeers;
+  int peer[kMaxRanks];
+  int64_t send_off[kMaxRanks + 1];
+};
+__global__ void __launch_bounds__(256)
+    halo_push_kernel(int64_t count, int recs, const uint32_t* __restrict__ send_idx,
+                     const uint32_t* __restrict__ remote_row, PushArgs pa, const D4* vel, const PeerDev* __restrict__ pd,
+                     LcpState* state, unsigned long long seq) {
+  if (state->done) return;
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k < count * recs) {
+    const int64_t e = k / recs;
+    const int r = static_cast<int>(k % recs);
+    int q = 0;
+    while (q + 1 < pa.npeers && e >= pa.send_off[q + 1]) ++q;
+    D4* dst = pd->vel[pa.peer[q]];
+    st256(dst + static_cast<int64_t>(remote_row[e]) * recs + r, ld256(vel + static_cast<int64_t>(send_idx[e]) * recs + r));
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t ticket = atomicAdd(&state->ticket2, 1u);
+    if (ticket == gridDim.x - 1) {
+      state->ticket2 = 0;
+      __threadfence_system();
+      for (int r = 0; r < pd->world; ++r)
+        if (r != pd->me) st_release_sys(&pd->ctrl[r]->halo_flag[pd->me], seq);
+    }
+  }
+}
+
 // MODE 0: initial pass (state holds gamma_0; g_0 = D^T M D gamma_0, residual only). MODE 1: iteration pass.
+// Multi-GPU with peer memory (a.peer != NULL): every CTA first waits until all other ranks have published velocity halo
+// a.halo_seq; the last CTA stores this rank's four totals into every rank's control block, publishes a.red_seq, waits for
+// the other ranks' totals and reduces them in rank order, so that every rank advances to the same alpha / done without
+// a collective call or a host round trip.
 template <bool SIX, int MODE>
 __global__ void __launch_bounds__(kRateThreads)
     rate_pass_kernel(LcpArgs a, int it, int first, const double2* __restrict__ st_prev, double2* __restrict__ st_cur) {
@@ -394,6 +470,13 @@ __global__ void __launch_bounds__(kRateThreads)
   const double alpha = (MODE == 1) ? a.state->alpha : 0.0;
   double res = -1.0, xx = 0.0, xg = 0.0, gg = 0.0;
   const int t = threadIdx.x;
+  if (a.peer) {
+    if (t < a.peer->world && t != a.peer->me && !wait_flag(&a.peer->ctrl[a.peer->me]->halo_flag[t], a.halo_seq)) {
+      a.state->error = 1;
+      a.state->done = 1;
+    }
+    __syncthreads();
+  }
   const int64_t stride = static_cast<int64_t>(gridDim.x) * kRateThreads;
   for (int64_t c = static_cast<int64_t>(blockIdx.x) * kRateThreads + t; c < a.npairs; c += stride) {
     const double2 sp = ldg128(st_prev + c);
@@ -460,7 +543,30 @@ __global__ void __launch_bounds__(kRateThreads)
   if (t == 0) {
     LcpState* s = a.state;
     s->ticket = 0;
-    if (a.red_local) {  // multi-GPU: the totals go through an all-gather, advance_kernel finishes the iteration
+    if (a.peer) {
+      const PeerDev* pd = a.peer;
+      const int me = pd->me, W = pd->world, par = static_cast<int>(a.red_seq & 1ull);
+      for (int r = 0; r < W; ++r) {
+        double* dst = pd->ctrl[r]->red[par][me];
+        dst[0] = res, dst[1] = xx, dst[2] = xg, dst[3] = gg;
+      }
+      __threadfence_system();
+      for (int r = 0; r < W; ++r) st_release_sys(&pd->ctrl[r]->red_flag[par][me], a.red_seq);
+      bool ok = true;
+      for (int r = 0; r < W; ++r) ok = wait_flag(&pd->ctrl[me]->red_flag[par][r], a.red_seq) && ok;
+      if (!ok) {
+        s->error = 1;
+        s->done = 1;
+      } else {
+        res = -1.0, xx = 0.0, xg = 0.0, gg = 0.0;
+        for (int r = 0; r < W; ++r) {  // rank order: the same sums on every rank
+          const double* src = pd->ctrl[me]->red[par][r];
+          res = fmax(res, ld_relaxed_sys(src));
+          xx += ld_relaxed_sys(src + 1), xg += ld_relaxed_sys(src + 2), gg += ld_relaxed_sys(src + 3);
+        }
+        advance_state(s, res, xx, xg, gg, it, MODE, a.fixed, a.tol, a.it_cap);
+      }
+    } else if (a.red_local) {  // multi-GPU over NCCL: the totals go through an all-gather, advance_kernel finishes
       a.red_local[0] = res, a.red_local[1] = xx, a.red_local[2] = xg, a.red_local[3] = gg;
     } else {
       advance_state(s, res, xx, xg, gg, it, MODE, a.fixed, a.tol, a.it_cap);
@@ -521,7 +627,8 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   MB200_TRY(s0.alloc(C, st));
   MB200_TRY(s1.alloc(C, st));
   MB200_TRY(partials.alloc(4 * static_cast<size_t>(rate_grid), st));
-  MB200_TRY(vel.alloc(static_cast<size_t>(six ? 2 : 1) * n, st));
+  const bool peer_mode = dist && dist->peer_dev;
+  if (!peer_mode) MB200_TRY(vel.alloc(static_cast<size_t>(six ? 2 : 1) * n, st));
   MB200_TRY(mob.alloc(n, st));
   MB200_TRY(state.alloc(1, st));
   MB200_CUDA(cudaMemsetAsync(state.p, 0, sizeof(LcpState), st));
@@ -530,7 +637,9 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   a.n = n, a.npairs = C;
   a.pairs = sys.pairs, a.rec = sys.rec, a.mob = mob.p;
   a.inc_ptr = inc.ptr.p, a.inc_list = inc.list.p;
-  a.vel = vel.p;
+  a.vel = peer_mode ? dist->vel_arena : vel.p;
+  a.peer = peer_mode ? dist->peer_dev : nullptr;
+  a.halo_seq = 0, a.red_seq = 0;
   a.mu = sys.mu, a.dt = sys.dt, a.tol = params->tol;
   a.fixed = fixed ? 1 : 0, a.it_cap = it_cap;
   a.state = state.p, a.partials = partials.p;
@@ -544,6 +653,18 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
     if (!dist) return MB200_OK;
     StageScope ps(MB200_STAGE_LCP_COMM, st);
     const int64_t ns = dist->send_off[dist->npeers], nr = dist->recv_off[dist->npeers];
+    if (peer_mode) {
+      PushArgs pa;
+      pa.npeers = dist->npeers;
+      for (int k = 0; k < kMaxRanks; ++k) pa.peer[k] = dist->peer[k];
+      for (int k = 0; k <= kMaxRanks; ++k) pa.send_off[k] = dist->send_off[k];
+      a.halo_seq = ++(*dist->halo_seq);
+      const int grid = ns > 0 ? grid_for(ns * recs, 256) : 1;
+      halo_push_kernel<<<grid, 256, 0, st>>>(ns, recs, dist->send_idx, dist->remote_row, pa, a.vel, dist->peer_dev, state.p,
+                                             a.halo_seq);
+      MB200_LAUNCHED();
+      return MB200_OK;
+    }
     if (ns > 0) {
       halo_pack_kernel<<<grid_for(ns * recs, 256), 256, 0, st>>>(ns, recs, dist->send_idx, vel.p, dist->sendbuf, state.p);
       MB200_LAUNCHED();
@@ -567,7 +688,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   };
   // multi-GPU: all-gather of the ranks' totals (rank order => identical sums everywhere), then the state update
   auto reduce = [&](int it_now, int mode) -> int {
-    if (!dist) return MB200_OK;
+    if (!dist || peer_mode) return MB200_OK;  // peer mode: the rate pass's last CTA has done it
     StageScope ps(MB200_STAGE_LCP_COMM, st);
     MB200_NCCL(nccl->AllGather(dist->red, dist->red + 4, 4, ncclDouble, dist->comm->comm, st));
     advance_kernel<<<1, 32, 0, st>>>(state.p, dist->red + 4, dist->comm->world, it_now, mode, a.fixed, a.tol, a.it_cap);
@@ -600,6 +721,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
     MB200_LAUNCHED();
   }
   MB200_TRY(halo());
+  if (peer_mode) a.red_seq = ++(*dist->red_seq);
   {
     StageScope ps(MB200_STAGE_LCP_RATE, st);
     if (six)
@@ -635,6 +757,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
         MB200_LAUNCHED();
       }
       MB200_TRY(halo());
+      if (peer_mode) a.red_seq = ++(*dist->red_seq);
       {
         StageScope ps(MB200_STAGE_LCP_RATE, st);
         if (six)
@@ -669,6 +792,10 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   MB200_CUDA(cudaMemcpyAsync(pinned.h, state.p, sizeof(LcpState), cudaMemcpyDeviceToHost, st));
   MB200_CUDA(cudaStreamSynchronize(st));
   hs = *pinned.h;
+  if (hs.error) {
+    set_error("multi-GPU exchange timed out: a peer rank did not publish its velocity halo / reduction totals");
+    return MB200_ERR_COMM;
+  }
   if (result_h) {
     result_h->max_abs_projected_sep = hs.res;
     result_h->ite_count = it_final;

@@ -123,6 +123,11 @@ class Comm:
         self._h = C.c_void_p()
         check(lib.mb200_comm_create(C.byref(self._h), self.world, self.rank, buf), "comm_create")
 
+    @property
+    def exchange_mode(self):
+        """'peer' (kernels store into the peers' memory over NVLink) or 'nccl'; decided at the first distributed step."""
+        return "peer" if lib.mb200_comm_exchange_mode(self._h) else "nccl"
+
     def __del__(self):
         if getattr(self, "_h", None) and lib is not None:
             lib.mb200_comm_destroy(self._h)

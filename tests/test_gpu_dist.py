@@ -83,11 +83,12 @@ def _rel(a, b):
     return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
 
 
-def _world_worker(rank, world, port, out):
+def _world_worker(rank, world, port, out, exchange):
     try:
         import torch.distributed as dist
         from mundy_b200 import dist as mbd
         os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+        os.environ["MB200_DIST_EXCHANGE"] = exchange
         torch.cuda.set_device(rank)
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
         dev = f"cuda:{rank}"
@@ -115,7 +116,9 @@ def _world_worker(rank, world, port, out):
             for x, y in zip(ref, got):
                 assert y[4] < TOL and x[4] < TOL and abs(y[3] - x[3]) <= max(2, x[3] // 3), (kind, x[3], y[3])
                 assert np.max(np.abs(y[0] - x[0])) <= 20 * TOL
-            msgs.append((kind, [g[2] for g in got], mbd.local_counts.__name__))
+            msgs.append((kind, [g[2] for g in got], comm.exchange_mode))
+        # "peer": the kernels exchanged through CUDA-IPC mapped memory (no silent fall back to NCCL on this box)
+        assert comm.exchange_mode == exchange, (comm.exchange_mode, exchange)
         out.put((rank, "ok", msgs))
         dist.destroy_process_group()
     except Exception as e:  # noqa: BLE001
@@ -123,14 +126,17 @@ def _world_worker(rank, world, port, out):
         out.put((rank, f"{type(e).__name__}: {e}\n{traceback.format_exc()}", None))
 
 
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])
 @pytest.mark.parametrize("world", [2])
-def test_two_gpu_step_matches_single_gpu(cuda, world):
+def test_two_gpu_step_matches_single_gpu(cuda, world, exchange):
+    """Both forms of the per-iteration exchange: peer memory (remote stores + system-scope flags from inside the kernels)
+    and NCCL send/recv + all-gather."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs (run with gpurun --gpus {world})")
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_world_worker, args=(r, world, port, out)) for r in range(world)]
+    procs = [ctx.Process(target=_world_worker, args=(r, world, port, out, exchange)) for r in range(world)]
     for p in procs:
         p.start()
     res = [out.get(timeout=600) for _ in procs]
