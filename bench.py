@@ -404,6 +404,7 @@ def run_b200(args):
     if comm is not None:
         nl, ng = mbd.local_counts(links)
         line["dist"] = {"rank0_local_bodies": nl, "rank0_ghost_rows": ng, "owned_per_rank": n,
+                        "exchange": comm.exchange_mode,
                         "note": "links_per_step, stages and roofline are rank 0's"}
     print(json.dumps(line))
     if dist is not None:

@@ -112,6 +112,34 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+__global__ void __launch_bounds__(256) owned_morton_kernel(int64_t n, const uint32_t* __restrict__ perm,
+                                                           const uint8_t* __restrict__ owned, uint8_t* __restrict__ out) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k < n) out[k] = owned[perm[k]];
+}
+
+// Per-body lists of ghost copies from the send list: count, (scan), fill. Entry e of the send list goes to peer q(e).
+struct SendOffsets {
+  int npeers;
+  int peer[16];
+  int64_t off[17];
+};
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+    push_lists_kernel(int64_t count, SendOffsets so, const uint32_t* __restrict__ send_idx,
+                      const uint32_t* __restrict__ remote_row, uint32_t* __restrict__ counts,
+                      const int64_t* __restrict__ ptr, uint32_t* __restrict__ dst) {
+  const int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (e >= count) return;
+  const uint32_t b = send_idx[e];
+  const uint32_t slot = atomicAdd(counts + b, 1u);
+  if (FILL) {
+    int q = 0;
+    while (q + 1 < so.npeers && e >= so.off[q + 1]) ++q;
+    dst[ptr[b] + slot] = (static_cast<uint32_t>(so.peer[q]) << 28) | remote_row[e];
+  }
+}
+
 __global__ void __launch_bounds__(256) invert_perm_kernel(int64_t n, const uint32_t* __restrict__ perm,
                                                           uint32_t* __restrict__ inv) {
   const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -300,6 +328,9 @@ int dist_build(cudaStream_t st, mb200_neighbor_links* h, mb200_comm* comm, const
   MB200_TRY(peer_setup(comm, st, 2 * N));
   if (comm->peer.ok) {
     const NcclApi* nccl = nccl_api();
+    MB200_TRY(D.owned_s.reserve(nl));
+    owned_morton_kernel<<<grid_for(nl, 256), 256, 0, st>>>(nl, h->perm.p, D.owned.p, D.owned_s.p);
+    MB200_LAUNCHED();
     MB200_TRY(D.remote_row.reserve(ns + 1));
     MB200_NCCL(nccl->GroupStart());
     for (int q = 0; q < D.npeers; ++q) {
@@ -308,6 +339,28 @@ int dist_build(cudaStream_t st, mb200_neighbor_links* h, mb200_comm* comm, const
       if (cs > 0) MB200_NCCL(nccl->Recv(D.remote_row.p + D.send_off[q], cs, ncclUint32, D.peer[q], comm->comm, st));
     }
     MB200_NCCL(nccl->GroupEnd());
+    // body-major form for the fused push of the body pass
+    MB200_REQUIRE(2 * N < (int64_t(1) << 28), "too many bodies for the 28-bit ghost row index");
+    Scratch<uint32_t> pcount;
+    MB200_TRY(pcount.alloc(nl, st));
+    MB200_TRY(D.push_ptr.reserve(nl + 1));
+    MB200_TRY(D.push_dst.reserve(ns + 1));
+    SendOffsets so;
+    so.npeers = D.npeers;
+    for (int q = 0; q < 16; ++q) so.peer[q] = D.peer[q];
+    for (int q = 0; q < 17; ++q) so.off[q] = D.send_off[q];
+    MB200_CUDA(cudaMemsetAsync(pcount.p, 0, nl * sizeof(uint32_t), st));
+    if (ns > 0) {
+      push_lists_kernel<false><<<grid_for(ns, 256), 256, 0, st>>>(ns, so, D.send_idx.p, D.remote_row.p, pcount.p, nullptr, nullptr);
+      MB200_LAUNCHED();
+    }
+    MB200_TRY(exclusive_scan_u32_to_i64(st, nl, pcount.p, D.push_ptr.p));
+    MB200_CUDA(cudaMemsetAsync(pcount.p, 0, nl * sizeof(uint32_t), st));
+    if (ns > 0) {
+      push_lists_kernel<true><<<grid_for(ns, 256), 256, 0, st>>>(ns, so, D.send_idx.p, D.remote_row.p, pcount.p, D.push_ptr.p,
+                                                                 D.push_dst.p);
+      MB200_LAUNCHED();
+    }
   }
   D.built = true;
   return MB200_OK;
@@ -388,7 +441,9 @@ extern "C" int mb200_collision_step_dist(mb200_neighbor_links* h, mb200_comm* co
   const bool peer_mode = comm->peer.ok;
   ds.peer_dev = peer_mode ? comm->peer.dev : nullptr;
   ds.vel_arena = peer_mode ? comm->peer.vel : nullptr;
-  ds.remote_row = peer_mode ? D.remote_row.p : nullptr;
+  ds.push_ptr = peer_mode ? D.push_ptr.p : nullptr;
+  ds.push_dst = peer_mode ? D.push_dst.p : nullptr;
+  ds.owned_s = peer_mode ? D.owned_s.p : nullptr;
   ds.halo_seq = &comm->peer.halo_seq, ds.red_seq = &comm->peer.red_seq;
   mb200_step_params p = *params;
   p.throw_on_max_iters = 0;  // reported through stats (every rank must finish the collective sequence)

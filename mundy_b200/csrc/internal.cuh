@@ -49,7 +49,9 @@ struct DistSolve {
   // peer-memory exchange (comm.cuh; peer_dev == NULL: the NCCL calls above are used)
   const struct PeerDev* peer_dev;      // device table of every rank's mapped control block and velocity arena
   D4* vel_arena;                       // this rank's velocity arena (the solver's velocity records live here)
-  const uint32_t* remote_row;          // [send list] row of the body in the destination rank's arena
+  const int64_t* push_ptr;             // [n + 1] per body: its entries in push_dst (owned boundary bodies only)
+  const uint32_t* push_dst;            // rank << 28 | row of the ghost copy in that rank's arena
+  const uint8_t* owned_s;              // [n] ownership flags in the solver's (Morton) body order
   unsigned long long* halo_seq;        // host counters kept in the communicator (monotone across solves)
   unsigned long long* red_seq;
 };

@@ -59,6 +59,12 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
   // rate pass consumes and of the reduction it produces
   const PeerDev* peer;
   unsigned long long halo_seq, red_seq;
+  // peer mode: [n] 1 = owned body. The body pass leaves the ghost rows of the velocity arena alone: their owners store
+  // into them from their own GPUs, possibly before this rank's body pass has run.
+  const uint8_t* owned;
+  // peer mode: per-body list of the ghost rows (rank << 28 | row in that rank's arena) that mirror an owned body
+  const int64_t* push_ptr;
+  const uint32_t* push_dst;
 };
 
 // ---- system-scope signalling between GPUs -----------------------------------------------------------------------
@@ -334,11 +340,28 @@ __global__ void __launch_bounds__(kBodyThreads)
       V3 u, w;
       body_mobility_axis(m, rod, V3{mr.x, mr.y, mr.z}, f, tq, u, w);
       if (!FINAL) {
-        if (SIX) {
-          st256(a.vel + 2 * b, D4{u.x, u.y, u.z, 0.0});
-          st256(a.vel + 2 * b + 1, D4{w.x, w.y, w.z, 0.0});
+        if (a.owned && !a.owned[b]) {
+          // ghost row: its owner stores into it from its own GPU (below, on that rank)
         } else {
-          st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
+          if (SIX) {
+            st256(a.vel + 2 * b, D4{u.x, u.y, u.z, 0.0});
+            st256(a.vel + 2 * b + 1, D4{w.x, w.y, w.z, 0.0});
+          } else {
+            st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
+          }
+          if (a.push_ptr) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
+            for (int64_t k = a.push_ptr[b], ke = a.push_ptr[b + 1]; k < ke; ++k) {
+              const uint32_t d = __ldg(a.push_dst + k);
+              D4* dst = a.peer->vel[d >> 28];
+              const int64_t row = d & 0x0fffffffu;
+              if (SIX) {
+                st256(dst + 2 * row, D4{u.x, u.y, u.z, 0.0});
+                st256(dst + 2 * row + 1, D4{w.x, w.y, w.z, 0.0});
+              } else {
+                st256(dst + row, D4{u.x, u.y, u.z, 0.0});
+              }
+            }
+          }
         }
       } else {
         speed = fmax(speed, sqrt(u.x * u.x + u.y * u.y + u.z * u.z));  // KokkosLCP.cpp:861-872 (collision velocity)
@@ -352,6 +375,21 @@ __global__ void __launch_bounds__(kBodyThreads)
     }
     cp_async_wait_all();  // next block's list and the block after's pointers have landed
     __syncthreads();
+  }
+  if (!FINAL && a.push_ptr) {
+    // every CTA's remote stores are ordered before the flag the last CTA publishes to all ranks (release, system scope);
+    // the consumers are the peers' rate_pass_kernels
+    __threadfence_system();
+    __syncthreads();
+    if (t == 0) {
+      const uint32_t ticket = atomicAdd(&a.state->ticket2, 1u);
+      if (ticket == gridDim.x - 1) {
+        a.state->ticket2 = 0;
+        __threadfence_system();
+        for (int r = 0; r < a.peer->world; ++r)
+          if (r != a.peer->me) st_release_sys(&a.peer->ctrl[r]->halo_flag[a.peer->me], a.halo_seq);
+      }
+    }
   }
   if (FINAL) {
     const double m = block_max(speed, sh, 0.0);
@@ -419,41 +457,6 @@ __global__ void __launch_bounds__(256) halo_unpack_kernel(int64_t count, int rec
   if (k >= count * recs) return;
   const int64_t b = idx[k / recs];
   vel[b * recs + (k % recs)] = buf[k];
-}
-
-// Peer-memory velocity halo: the owners' records are stored straight into the ghost rows of the peers' velocity arenas
-// over NVLink (no staging buffer, no NCCL call); the last CTA to finish publishes the sequence number to every rank
-// with a system-scope release store. The consumer is the peers' rate_pass_kernel.
-struct PushArgs {
-  int npeers;
-  int peer[kMaxRanks];
-  int64_t send_off[kMaxRanks + 1];
-};
-__global__ void __launch_bounds__(256)
-    halo_push_kernel(int64_t count, int recs, const uint32_t* __restrict__ send_idx,
-                     const uint32_t* __restrict__ remote_row, PushArgs pa, const D4* vel, const PeerDev* __restrict__ pd,
-                     LcpState* state, unsigned long long seq) {
-  if (state->done) return;
-  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (k < count * recs) {
-    const int64_t e = k / recs;
-    const int r = static_cast<int>(k % recs);
-    int q = 0;
-    while (q + 1 < pa.npeers && e >= pa.send_off[q + 1]) ++q;
-    D4* dst = pd->vel[pa.peer[q]];
-    st256(dst + static_cast<int64_t>(remote_row[e]) * recs + r, ld256(vel + static_cast<int64_t>(send_idx[e]) * recs + r));
-  }
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t ticket = atomicAdd(&state->ticket2, 1u);
-    if (ticket == gridDim.x - 1) {
-      state->ticket2 = 0;
-      __threadfence_system();
-      for (int r = 0; r < pd->world; ++r)
-        if (r != pd->me) st_release_sys(&pd->ctrl[r]->halo_flag[pd->me], seq);
-    }
-  }
 }
 
 // MODE 0: initial pass (state holds gamma_0; g_0 = D^T M D gamma_0, residual only). MODE 1: iteration pass.
@@ -640,6 +643,9 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   a.vel = peer_mode ? dist->vel_arena : vel.p;
   a.peer = peer_mode ? dist->peer_dev : nullptr;
   a.halo_seq = 0, a.red_seq = 0;
+  a.owned = peer_mode ? dist->owned_s : nullptr;
+  a.push_ptr = peer_mode ? dist->push_ptr : nullptr;
+  a.push_dst = peer_mode ? dist->push_dst : nullptr;
   a.mu = sys.mu, a.dt = sys.dt, a.tol = params->tol;
   a.fixed = fixed ? 1 : 0, a.it_cap = it_cap;
   a.state = state.p, a.partials = partials.p;
@@ -650,21 +656,9 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   const int recs = six ? 2 : 1;
   // multi-GPU: ghost rows of the velocity records come from their owners after every body pass
   auto halo = [&]() -> int {
-    if (!dist) return MB200_OK;
+    if (!dist || peer_mode) return MB200_OK;  // peer mode: the body pass has pushed the records itself
     StageScope ps(MB200_STAGE_LCP_COMM, st);
     const int64_t ns = dist->send_off[dist->npeers], nr = dist->recv_off[dist->npeers];
-    if (peer_mode) {
-      PushArgs pa;
-      pa.npeers = dist->npeers;
-      for (int k = 0; k < kMaxRanks; ++k) pa.peer[k] = dist->peer[k];
-      for (int k = 0; k <= kMaxRanks; ++k) pa.send_off[k] = dist->send_off[k];
-      a.halo_seq = ++(*dist->halo_seq);
-      const int grid = ns > 0 ? grid_for(ns * recs, 256) : 1;
-      halo_push_kernel<<<grid, 256, 0, st>>>(ns, recs, dist->send_idx, dist->remote_row, pa, a.vel, dist->peer_dev, state.p,
-                                             a.halo_seq);
-      MB200_LAUNCHED();
-      return MB200_OK;
-    }
     if (ns > 0) {
       halo_pack_kernel<<<grid_for(ns * recs, 256), 256, 0, st>>>(ns, recs, dist->send_idx, vel.p, dist->sendbuf, state.p);
       MB200_LAUNCHED();
@@ -712,6 +706,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   }
 
   // initial residual: s1 = {gamma_0, g_0 = D^T M D gamma_0}
+  if (peer_mode) a.halo_seq = ++(*dist->halo_seq);
   {
     StageScope ps(MB200_STAGE_LCP_BODY, st);
     if (six)
@@ -748,6 +743,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
       const double2* prev = odd ? s1.p : s0.p;
       double2* cur = odd ? s0.p : s1.p;
       const int first = it == 1 ? 1 : 0;
+      if (peer_mode) a.halo_seq = ++(*dist->halo_seq);
       {
         StageScope ps(MB200_STAGE_LCP_BODY, st);
         if (six)

@@ -38,7 +38,10 @@ struct mb200_neighbor_links {
     mb200::DevBuf<uint8_t> counted;    // contact counted by this rank                 [npairs]
     mb200::DevBuf<uint32_t> inv_perm;  // local caller index -> Morton index           [n_local]
     mb200::DevBuf<uint32_t> send_idx, recv_idx;
+    mb200::DevBuf<uint8_t> owned_s;      // ownership flags in Morton order (peer-memory mode)
     mb200::DevBuf<uint32_t> remote_row;  // [send list] destination rows in the peers' velocity arenas (peer-memory mode)
+    mb200::DevBuf<int64_t> push_ptr;     // [n_local + 1] body -> its ghost copies (Morton order)
+    mb200::DevBuf<uint32_t> push_dst;    // rank << 28 | row
     mb200::DevBuf<mb200::D4> sendbuf, recvbuf;
     mb200::DevBuf<double> red;
     mb200::DevBuf<int32_t> flag_all;
