@@ -116,7 +116,7 @@ struct DevBuf {
     if (n <= cap) return MB200_OK;
     if (p) MB200_CUDA(cudaFree(p));
     p = nullptr;
-    size_t want = n + n / 8 + 64;
+    size_t want = n + n / 4 + 64;  // headroom: cudaFree + cudaMalloc of a large buffer costs milliseconds (more with peer mappings)
     MB200_CUDA(cudaMalloc(reinterpret_cast<void**>(&p), want * sizeof(T)));
     cap = want;
     return MB200_OK;

@@ -268,7 +268,13 @@ __global__ void __launch_bounds__(kBodyThreads)
     const int64_t b0 = blk * kBodiesPerCta;
     const int nb = bodies_in(blk);
     D4 mr{0.0, 0.0, 1.0, -1.0};
-    if (t < nb) mr = ldg256(a.mob + b0 + t);  // needed only at the end: issued now to overlap with the gathers
+    int64_t pk = 0, pke = 0;
+    bool own = true;
+    if (t < nb) {
+      mr = ldg256(a.mob + b0 + t);  // needed only at the end: issued now to overlap with the gathers
+      if (!FINAL && a.owned) own = __ldg(a.owned + b0 + t) != 0;
+      if (!FINAL && a.push_ptr) pk = __ldg(a.push_ptr + b0 + t), pke = __ldg(a.push_ptr + b0 + t + 1);
+    }
     const int64_t e_begin = s_ptr[pcur][0], e_end = s_ptr[pcur][nb];
     int64_t my_beg = 0, my_end = 0;
     if (t < nb) my_beg = s_ptr[pcur][t], my_end = s_ptr[pcur][t + 1];
@@ -340,7 +346,7 @@ __global__ void __launch_bounds__(kBodyThreads)
       V3 u, w;
       body_mobility_axis(m, rod, V3{mr.x, mr.y, mr.z}, f, tq, u, w);
       if (!FINAL) {
-        if (a.owned && !a.owned[b]) {
+        if (!own) {
           // ghost row: its owner stores into it from its own GPU (below, on that rank)
         } else {
           if (SIX) {
@@ -350,7 +356,7 @@ __global__ void __launch_bounds__(kBodyThreads)
             st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
           }
           if (a.push_ptr) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
-            for (int64_t k = a.push_ptr[b], ke = a.push_ptr[b + 1]; k < ke; ++k) {
+            for (int64_t k = pk; k < pke; ++k) {
               const uint32_t d = __ldg(a.push_dst + k);
               D4* dst = a.peer->vel[d >> 28];
               const int64_t row = d & 0x0fffffffu;
