@@ -71,6 +71,9 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
 __device__ inline void st_release_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+__device__ inline void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ inline unsigned long long ld_acquire_sys(const unsigned long long* p) {
   unsigned long long v;
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -385,16 +388,18 @@ __global__ void __launch_bounds__(kBodyThreads)
   if (!FINAL && a.push_ptr) {
     // every CTA's remote stores are ordered before the flag the last CTA publishes to all ranks (release, system scope);
     // the consumers are the peers' rate_pass_kernels
-    __threadfence_system();
+    // (bar.sync orders the CTA's stores before thread 0's system-scope fence: the grid-sync pattern, one fence per CTA)
     __syncthreads();
     if (t == 0) {
+      __threadfence_system();
       const uint32_t ticket = atomicAdd(&a.state->ticket2, 1u);
-      if (ticket == gridDim.x - 1) {
-        a.state->ticket2 = 0;
-        __threadfence_system();
-        for (int r = 0; r < a.peer->world; ++r)
-          if (r != a.peer->me) st_release_sys(&a.peer->ctrl[r]->halo_flag[a.peer->me], a.halo_seq);
-      }
+      sh[32] = (ticket == gridDim.x - 1) ? 1.0 : 0.0;
+      if (ticket == gridDim.x - 1) a.state->ticket2 = 0;
+    }
+    __syncthreads();
+    if (sh[32] != 0.0 && t < a.peer->world && t != a.peer->me) {  // one lane per rank: the flags leave in parallel
+      __threadfence_system();
+      st_relaxed_sys(&a.peer->ctrl[t]->halo_flag[a.peer->me], a.halo_seq);
     }
   }
   if (FINAL) {
@@ -549,21 +554,26 @@ __global__ void __launch_bounds__(kRateThreads)
     xg = block_sum(xg, sh);
     gg = block_sum(gg, sh);
   }
-  if (t == 0) {
-    LcpState* s = a.state;
-    s->ticket = 0;
-    if (a.peer) {
-      const PeerDev* pd = a.peer;
-      const int me = pd->me, W = pd->world, par = static_cast<int>(a.red_seq & 1ull);
-      for (int r = 0; r < W; ++r) {
-        double* dst = pd->ctrl[r]->red[par][me];
-        dst[0] = res, dst[1] = xx, dst[2] = xg, dst[3] = gg;
-      }
+  if (a.peer) {
+    // one lane per rank: this rank's totals into rank r's control block, fence, flag; then wait for rank r's totals here
+    __shared__ double s_tot[4];
+    __shared__ int s_bad;
+    if (t == 0) s_tot[0] = res, s_tot[1] = xx, s_tot[2] = xg, s_tot[3] = gg, s_bad = 0;
+    __syncthreads();
+    const PeerDev* pd = a.peer;
+    const int me = pd->me, W = pd->world, par = static_cast<int>(a.red_seq & 1ull);
+    if (t < W) {
+      double* dst = pd->ctrl[t]->red[par][me];
+      dst[0] = s_tot[0], dst[1] = s_tot[1], dst[2] = s_tot[2], dst[3] = s_tot[3];
       __threadfence_system();
-      for (int r = 0; r < W; ++r) st_release_sys(&pd->ctrl[r]->red_flag[par][me], a.red_seq);
-      bool ok = true;
-      for (int r = 0; r < W; ++r) ok = wait_flag(&pd->ctrl[me]->red_flag[par][r], a.red_seq) && ok;
-      if (!ok) {
+      st_relaxed_sys(&pd->ctrl[t]->red_flag[par][me], a.red_seq);
+      if (!wait_flag(&pd->ctrl[me]->red_flag[par][t], a.red_seq)) s_bad = 1;
+    }
+    __syncthreads();
+    if (t == 0) {
+      LcpState* s = a.state;
+      s->ticket = 0;
+      if (s_bad) {
         s->error = 1;
         s->done = 1;
       } else {
@@ -575,7 +585,13 @@ __global__ void __launch_bounds__(kRateThreads)
         }
         advance_state(s, res, xx, xg, gg, it, MODE, a.fixed, a.tol, a.it_cap);
       }
-    } else if (a.red_local) {  // multi-GPU over NCCL: the totals go through an all-gather, advance_kernel finishes
+    }
+    return;
+  }
+  if (t == 0) {
+    LcpState* s = a.state;
+    s->ticket = 0;
+    if (a.red_local) {  // multi-GPU over NCCL: the totals go through an all-gather, advance_kernel finishes
       a.red_local[0] = res, a.red_local[1] = xx, a.red_local[2] = xg, a.red_local[3] = gg;
     } else {
       advance_state(s, res, xx, xg, gg, it, MODE, a.fixed, a.tol, a.it_cap);
