@@ -5,7 +5,8 @@
 //       R0 = {nx, ny, nz, phi0}                       3-DOF and 6-DOF
 //       R1 = {arm_i.x, arm_i.y, arm_i.z, (i, j)}      6-DOF only; the int32 pair rides in the 4th slot
 //       R2 = {arm_j.x, arm_j.y, arm_j.z, 0}           6-DOF only
-//     stored interleaved: rec[3 c + k] (6-DOF) or rec[c] (3-DOF; the pair comes from the int2 list)
+//     stored as three arrays, one per record kind: rec[k C + c] (6-DOF) or rec[c] (3-DOF; the pair comes from the int2
+//     list), so that a warp reading consecutive contacts touches 8 lines per load instead of 24
 //   contact state {gamma, g} as double2, ping-pong between two buffers (no roll-forward copies, K13)
 //   body mobility record {axis.x, axis.y, axis.z, +r (rod) | -r (sphere)}, axis = q (x) z_hat, built once per solve
 //   body velocity records {U, 0} (+ {W, 0} for 6-DOF): 64 MB at 10^6 rods, gathered by the contact pass out of L2
@@ -68,9 +69,6 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
 };
 
 // ---- system-scope signalling between GPUs -----------------------------------------------------------------------
-__device__ inline void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
 __device__ inline void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
@@ -149,9 +147,9 @@ __global__ void __launch_bounds__(256)
   if (SIX) {
     const int2 p = pairs[c];
     const V3 ai = ld3(arm_i, c), aj = ld3(arm_j, c);
-    st256(rec + 3 * c, D4{n.x, n.y, n.z, phi0[c]});
-    st256(rec + 3 * c + 1, D4{ai.x, ai.y, ai.z, pair_bits(p.x, p.y)});
-    st256(rec + 3 * c + 2, D4{aj.x, aj.y, aj.z, 0.0});
+    st256(rec + c, D4{n.x, n.y, n.z, phi0[c]});
+    st256(rec + npairs + c, D4{ai.x, ai.y, ai.z, pair_bits(p.x, p.y)});
+    st256(rec + 2 * npairs + c, D4{aj.x, aj.y, aj.z, 0.0});
   } else {
     st256(rec + c, D4{n.x, n.y, n.z, phi0[c]});
   }
@@ -163,7 +161,7 @@ __global__ void __launch_bounds__(256)
                            double* __restrict__ phi0, double* __restrict__ gamma) {
   const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (c >= npairs) return;
-  if (phi0) phi0[c] = ldg256(rec + (SIX ? 3 * c : c)).w;
+  if (phi0) phi0[c] = ldg256(rec + c).w;
   if (gamma) gamma[c] = state[c].x;
 }
 
@@ -180,14 +178,14 @@ __global__ void __launch_bounds__(256)
                           const double* __restrict__ W_ext, double dt) {
   const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (c >= npairs) return;
-  D4* r0p = rec + (SIX ? 3 * c : c);
+  D4* r0p = rec + c;
   D4 r0 = ld256(r0p);
   const V3 n{r0.x, r0.y, r0.z};
   V3 wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
   int2 p;
   const bool six = SIX && W_ext;
   if (SIX) {
-    const D4 r1 = ld256(rec + 3 * c + 1), r2 = ld256(rec + 3 * c + 2);
+    const D4 r1 = ld256(rec + npairs + c), r2 = ld256(rec + 2 * npairs + c);
     p = pair_of(r1);
     ai = V3{r1.x, r1.y, r1.z}, aj = V3{r2.x, r2.y, r2.z};
     if (six) wi = ld3(W_ext, p.x), wj = ld3(W_ext, p.y);
@@ -215,6 +213,56 @@ __device__ inline void cp_async8(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
 }
 __device__ inline void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// End of a body's pass: U = M F from the summed wrench; velocity records (and, multi-GPU, their ghost copies on the
+// peers) or, in the FINAL pass, the solver's outputs.
+template <bool SIX, bool FINAL>
+__device__ inline void body_epilogue(const LcpArgs& a, int64_t b, const double* acc, const D4& mr, bool own, int64_t pk,
+                                     int64_t pke, double& speed, double* __restrict__ F, double* __restrict__ T,
+                                     double* __restrict__ U, double* __restrict__ W, const double* __restrict__ U_ext,
+                                     const double* __restrict__ W_ext) {
+  {
+      const bool rod = SIX && mr.w > 0.0;
+      const Mob m = mobility_of(fabs(mr.w), a.mu);
+      const V3 f{acc[0], acc[1], acc[2]};
+      const V3 tq = SIX ? V3{acc[3], acc[4], acc[5]} : V3{0.0, 0.0, 0.0};
+      V3 u, w;
+      body_mobility_axis(m, rod, V3{mr.x, mr.y, mr.z}, f, tq, u, w);
+      if (!FINAL) {
+        if (!own) {
+          // ghost row: its owner stores into it from its own GPU (below, on that rank)
+        } else {
+          if (SIX) {
+            st256(a.vel + 2 * b, D4{u.x, u.y, u.z, 0.0});
+            st256(a.vel + 2 * b + 1, D4{w.x, w.y, w.z, 0.0});
+          } else {
+            st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
+          }
+          if (a.push_ptr) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
+            for (int64_t k = pk; k < pke; ++k) {
+              const uint32_t d = __ldg(a.push_dst + k);
+              D4* dst = a.peer->vel[d >> 28];
+              const int64_t row = d & 0x0fffffffu;
+              if (SIX) {
+                st256(dst + 2 * row, D4{u.x, u.y, u.z, 0.0});
+                st256(dst + 2 * row + 1, D4{w.x, w.y, w.z, 0.0});
+              } else {
+                st256(dst + row, D4{u.x, u.y, u.z, 0.0});
+              }
+            }
+          }
+        }
+      } else {
+        speed = fmax(speed, sqrt(u.x * u.x + u.y * u.y + u.z * u.z));  // KokkosLCP.cpp:861-872 (collision velocity)
+        if (F) st3(F, b, f);
+        if (SIX && T) st3(T, b, tq);
+        if (U_ext) u = u + ld3(U_ext, b);  // U += U_col on top of the external velocity (NGPSpheresLCP.cpp:867-877)
+        if (SIX && W_ext) w = w + ld3(W_ext, b);
+        if (U) st3(U, b, u);
+        if (SIX && W) st3(W, b, w);
+      }
+    }
+}
 
 // MODE 0: gamma is read from the state (initial pass and final pass). MODE 1: gamma re-derived from the previous state.
 // FINAL: also writes F,T,U,W in the solver's body order and reduces max |U| into state->vmax (single launch at the end).
@@ -304,8 +352,8 @@ __global__ void __launch_bounds__(kBodyThreads)
           if (e[u] != 0xffffffffu) {
             const int64_t c = e[u] >> 1;
             sp[u] = ldg128(st_prev + c);
-            r0[u] = ldg256(a.rec + (SIX ? 3 * c : c));
-            if (SIX) ra[u] = ldg256(a.rec + 3 * c + 1 + (e[u] & 1u));
+            r0[u] = ldg256(a.rec + c);
+            if (SIX) ra[u] = ldg256(a.rec + (1 + (e[u] & 1u)) * a.npairs + c);
           }
         }
 #pragma unroll
@@ -340,48 +388,8 @@ __global__ void __launch_bounds__(kBodyThreads)
       __syncthreads();
     }
 
-    if (t < nb) {
-      const int64_t b = b0 + t;
-      const bool rod = SIX && mr.w > 0.0;
-      const Mob m = mobility_of(fabs(mr.w), a.mu);
-      const V3 f{acc[0], acc[1], acc[2]};
-      const V3 tq = SIX ? V3{acc[3], acc[4], acc[5]} : V3{0.0, 0.0, 0.0};
-      V3 u, w;
-      body_mobility_axis(m, rod, V3{mr.x, mr.y, mr.z}, f, tq, u, w);
-      if (!FINAL) {
-        if (!own) {
-          // ghost row: its owner stores into it from its own GPU (below, on that rank)
-        } else {
-          if (SIX) {
-            st256(a.vel + 2 * b, D4{u.x, u.y, u.z, 0.0});
-            st256(a.vel + 2 * b + 1, D4{w.x, w.y, w.z, 0.0});
-          } else {
-            st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
-          }
-          if (a.push_ptr) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
-            for (int64_t k = pk; k < pke; ++k) {
-              const uint32_t d = __ldg(a.push_dst + k);
-              D4* dst = a.peer->vel[d >> 28];
-              const int64_t row = d & 0x0fffffffu;
-              if (SIX) {
-                st256(dst + 2 * row, D4{u.x, u.y, u.z, 0.0});
-                st256(dst + 2 * row + 1, D4{w.x, w.y, w.z, 0.0});
-              } else {
-                st256(dst + row, D4{u.x, u.y, u.z, 0.0});
-              }
-            }
-          }
-        }
-      } else {
-        speed = fmax(speed, sqrt(u.x * u.x + u.y * u.y + u.z * u.z));  // KokkosLCP.cpp:861-872 (collision velocity)
-        if (F) st3(F, b, f);
-        if (SIX && T) st3(T, b, tq);
-        if (U_ext) u = u + ld3(U_ext, b);  // U += U_col on top of the external velocity (NGPSpheresLCP.cpp:867-877)
-        if (SIX && W_ext) w = w + ld3(W_ext, b);
-        if (U) st3(U, b, u);
-        if (SIX && W) st3(W, b, w);
-      }
-    }
+    if (t < nb)
+      body_epilogue<SIX, FINAL>(a, b0 + t, acc, mr, own, pk, pke, speed, F, T, U, W, U_ext, W_ext);
     cp_async_wait_all();  // next block's list and the block after's pointers have landed
     __syncthreads();
   }
@@ -494,11 +502,11 @@ __global__ void __launch_bounds__(kRateThreads)
   const int64_t stride = static_cast<int64_t>(gridDim.x) * kRateThreads;
   for (int64_t c = static_cast<int64_t>(blockIdx.x) * kRateThreads + t; c < a.npairs; c += stride) {
     const double2 sp = ldg128(st_prev + c);
-    const D4 r0 = ldg256(a.rec + (SIX ? 3 * c : c));
+    const D4 r0 = ldg256(a.rec + c);
     const V3 n{r0.x, r0.y, r0.z};
     V3 ui, uj, wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
     if (SIX) {
-      const D4 r1 = ldg256(a.rec + 3 * c + 1), r2 = ldg256(a.rec + 3 * c + 2);
+      const D4 r1 = ldg256(a.rec + a.npairs + c), r2 = ldg256(a.rec + 2 * a.npairs + c);
       const int2 p = pair_of(r1);
       const D4 v0 = ldg256(a.vel + 2 * p.x), v1 = ldg256(a.vel + 2 * p.x + 1);
       const D4 v2 = ldg256(a.vel + 2 * p.y), v3 = ldg256(a.vel + 2 * p.y + 1);
@@ -712,6 +720,22 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
     return MB200_OK;
   };
 
+  // MODE 0 (state holds gamma) / 1 (gamma re-derived), FINAL (outputs instead of velocity records)
+  auto launch_body = [&](int mode, bool fin_pass, int first_it, const double2* stp, double* Fo, double* To, double* Uo,
+                         double* Wo) {
+#define MB200_BODY(KERNEL, SIX)                                                                                      \
+  do {                                                                                                               \
+    if (fin_pass)                                                                                                    \
+      KERNEL<SIX, 0, true><<<body_grid, kBodyThreads, 0, st>>>(a, first_it, stp, Fo, To, Uo, Wo, nullptr, nullptr);  \
+    else if (mode == 0)                                                                                              \
+      KERNEL<SIX, 0, false><<<body_grid, kBodyThreads, 0, st>>>(a, first_it, stp, Fo, To, Uo, Wo, nullptr, nullptr); \
+    else                                                                                                             \
+      KERNEL<SIX, 1, false><<<body_grid, kBodyThreads, 0, st>>>(a, first_it, stp, Fo, To, Uo, Wo, nullptr, nullptr); \
+  } while (0)
+    if (six) MB200_BODY(body_pass_kernel, true); else MB200_BODY(body_pass_kernel, false);
+#undef MB200_BODY
+  };
+
   {
     StageScope ps(MB200_STAGE_LCP_SETUP, st);
     mobility_records_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, sys.radius, sys.quat, sys.kind, mob.p);
@@ -731,10 +755,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   if (peer_mode) a.halo_seq = ++(*dist->halo_seq);
   {
     StageScope ps(MB200_STAGE_LCP_BODY, st);
-    if (six)
-      body_pass_kernel<true, 0, false><<<body_grid, kBodyThreads, 0, st>>>(a, 0, s0.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
-    else
-      body_pass_kernel<false, 0, false><<<body_grid, kBodyThreads, 0, st>>>(a, 0, s0.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+    launch_body(0, false, 0, s0.p, nullptr, nullptr, nullptr, nullptr);
     MB200_LAUNCHED();
   }
   MB200_TRY(halo());
@@ -768,10 +789,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
       if (peer_mode) a.halo_seq = ++(*dist->halo_seq);
       {
         StageScope ps(MB200_STAGE_LCP_BODY, st);
-        if (six)
-          body_pass_kernel<true, 1, false><<<body_grid, kBodyThreads, 0, st>>>(a, first, prev, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
-        else
-          body_pass_kernel<false, 1, false><<<body_grid, kBodyThreads, 0, st>>>(a, first, prev, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+        launch_body(1, false, first, prev, nullptr, nullptr, nullptr, nullptr);
         MB200_LAUNCHED();
       }
       MB200_TRY(halo());
@@ -794,10 +812,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   const double2* fin = (it_final & 1) ? s0.p : s1.p;
   {
     StageScope ps(MB200_STAGE_LCP_BODY, st);
-    if (six)
-      body_pass_kernel<true, 0, true><<<body_grid, kBodyThreads, 0, st>>>(a, 0, fin, F, T, U, W, nullptr, nullptr);
-    else
-      body_pass_kernel<false, 0, true><<<body_grid, kBodyThreads, 0, st>>>(a, 0, fin, F, nullptr, U, nullptr, nullptr, nullptr);
+    launch_body(0, true, 0, fin, F, six ? T : nullptr, U, six ? W : nullptr);
     MB200_LAUNCHED();
   }
   if (gamma_out || phi0_out) {

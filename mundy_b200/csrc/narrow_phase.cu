@@ -81,7 +81,8 @@ __global__ void __launch_bounds__(kTile)
   }
 }
 
-// Same arithmetic, written as solver contact records (lcp_solve.cu): R0 = {n, phi0}, R1 = {arm_i, (i,j)}, R2 = {arm_j, 0}.
+// Same arithmetic, written as solver contact records (lcp_solve.cu): R0 = {n, phi0}, R1 = {arm_i, (i,j)}, R2 = {arm_j, 0},
+// one array per record kind: rec[k * npairs + c].
 template <bool RODS, bool SIX>
 __global__ void __launch_bounds__(256)
     narrow_phase_rec_kernel(int64_t npairs, const int2* __restrict__ pairs, const uint32_t* __restrict__ perm,
@@ -109,9 +110,9 @@ __global__ void __launch_bounds__(256)
   }
   if (SIX) {
     const long long bits = (static_cast<long long>(p.y) << 32) | static_cast<long long>(static_cast<uint32_t>(p.x));
-    st256(rec + 3 * c, D4{g.n.x, g.n.y, g.n.z, g.sep});
-    st256(rec + 3 * c + 1, D4{g.arm_i.x, g.arm_i.y, g.arm_i.z, __longlong_as_double(bits)});
-    st256(rec + 3 * c + 2, D4{g.arm_j.x, g.arm_j.y, g.arm_j.z, 0.0});
+    st256(rec + c, D4{g.n.x, g.n.y, g.n.z, g.sep});
+    st256(rec + npairs + c, D4{g.arm_i.x, g.arm_i.y, g.arm_i.z, __longlong_as_double(bits)});
+    st256(rec + 2 * npairs + c, D4{g.arm_j.x, g.arm_j.y, g.arm_j.z, 0.0});
   } else {
     st256(rec + c, D4{g.n.x, g.n.y, g.n.z, g.sep});
   }
