@@ -8,6 +8,8 @@
 //   Scalar distance([tag,] LineSegment, LineSegment, cp1, cp2, s, t, sep)                distance/LineSegmentLineSegment.hpp:189-318
 //   Scalar distance([tag,] Point, LineSegment, cp, t, sep)                               distance/PointLineSegment.hpp:128-172
 //   Scalar distance([tag,] LineSegment, Sphere, cp, t, sep)                              distance/LineSegmentSphere.hpp:86-99
+//   PeriodicScaledMetric / PeriodicMetricX,Y,XY,YZ: sep, wrap; unwrap_points_to_ref(Point | Sphere | Spherocylinder |
+//   LineSegment, metric, ref)                                                            periodicity.hpp:335-845,1333-1516
 // Value types mirror primitives/{Point,Sphere,Spherocylinder,SpherocylinderSegment,LineSegment,AABB}.hpp accessors.
 // The single-object overloads run on the device through a one-element batch (they exist so that code and tests written
 // against the reference compile unchanged); bulk work should use the *_batch functions, which take device arrays in the
@@ -212,6 +214,64 @@ inline double distance(const LineSegment& seg, const Sphere& sph, Point& cp, dou
         "mb200_distance_segment_sphere");
   cp = detail::down3(cpd), sep = detail::down3(sv), t = dt.to_host()[0];
   return d.to_host()[0];
+}
+
+// ---- periodic metrics (periodicity.hpp) ------------------------------------------------------------------------------
+/// Orthorhombic periodic metric. All three axes periodic = geom::PeriodicScaledMetric (periodicity.hpp:743-845); the
+/// factories below give the partially periodic PeriodicMetricX / Y / XY / YZ (:335-741). cell_size()[d] <= 0: free axis.
+class PeriodicScaledMetric {
+ public:
+  explicit PeriodicScaledMetric(const Vector3& cell_size) : cell_{cell_size[0], cell_size[1], cell_size[2]} {}
+  bool is_periodic(unsigned d) const { return cell_[d] > 0.0; }
+  unsigned num_periodic_dimensions() const { return unsigned(is_periodic(0)) + is_periodic(1) + is_periodic(2); }
+  const double* cell_size() const { return cell_; }
+  /// Minimum-image separation vector from point1 to point2 (:814-818).
+  Vector3 sep(const Point& point1, const Point& point2) const {
+    auto a = detail::up3(point1), b = detail::up3(point2);
+    DeviceVector<double> out(3);
+    check(mb200_periodic_sep(nullptr, 1, cell_, a.data(), b.data(), out.data()), "mb200_periodic_sep");
+    return detail::down3(out);
+  }
+  /// Wrap a point into the primary cell (:821-824).
+  Point wrap(const Point& point) const {
+    auto a = detail::up3(point);
+    DeviceVector<double> out(3);
+    check(mb200_periodic_wrap(nullptr, 1, cell_, a.data(), out.data()), "mb200_periodic_wrap");
+    return detail::down3(out);
+  }
+
+ private:
+  double cell_[3];
+};
+inline PeriodicScaledMetric periodic_scaled_metric_from_unit_cell(const Vector3& cell_size) {  // :870-874
+  return PeriodicScaledMetric(cell_size);
+}
+inline PeriodicScaledMetric PeriodicMetricX(double wx) { return PeriodicScaledMetric({wx, 0.0, 0.0}); }
+inline PeriodicScaledMetric PeriodicMetricY(double wy) { return PeriodicScaledMetric({0.0, wy, 0.0}); }
+inline PeriodicScaledMetric PeriodicMetricXY(double wx, double wy) { return PeriodicScaledMetric({wx, wy, 0.0}); }
+inline PeriodicScaledMetric PeriodicMetricYZ(double wy, double wz) { return PeriodicScaledMetric({0.0, wy, wz}); }
+
+/// unwrap_points_to_ref (:1333-1339 points; :1487-1516 spheres / spherocylinders move their centre; :1368-1382 segments).
+inline Point unwrap_points_to_ref(const Point& point, const PeriodicScaledMetric& metric, const Point& ref_point) {
+  auto a = detail::up3(point), r = detail::up3(ref_point);
+  DeviceVector<double> out(3);
+  check(mb200_periodic_unwrap_points(nullptr, 1, metric.cell_size(), a.data(), r.data(), out.data()),
+        "mb200_periodic_unwrap_points");
+  return detail::down3(out);
+}
+inline Sphere unwrap_points_to_ref(const Sphere& s, const PeriodicScaledMetric& metric, const Point& ref_point) {
+  return Sphere(unwrap_points_to_ref(s.center(), metric, ref_point), s.radius());
+}
+inline Spherocylinder unwrap_points_to_ref(const Spherocylinder& s, const PeriodicScaledMetric& metric,
+                                           const Point& ref_point) {
+  return Spherocylinder(unwrap_points_to_ref(s.center(), metric, ref_point), s.orientation(), s.radius(), s.length());
+}
+inline LineSegment unwrap_points_to_ref(const LineSegment& seg, const PeriodicScaledMetric& metric, const Point& ref_point) {
+  auto a = detail::up3(seg.start()), b = detail::up3(seg.end()), r = detail::up3(ref_point);
+  DeviceVector<double> o0(3), o1(3);
+  check(mb200_periodic_unwrap_segments(nullptr, 1, metric.cell_size(), a.data(), b.data(), r.data(), o0.data(), o1.data()),
+        "mb200_periodic_unwrap_segments");
+  return LineSegment(detail::down3(o0), detail::down3(o1));
 }
 
 }  // namespace geom

@@ -10,6 +10,7 @@
 #define MUNDY_B200_NEIGHBOR_LINKS_HPP_
 
 #include "core.hpp"
+#include "geom.hpp"
 
 namespace mundy_b200 {
 namespace mesh {
@@ -70,6 +71,14 @@ class GenNeighborLinks {
   GenNeighborLinks& set_search_buffer(double buffer) {
     require_open("Cannot set search buffer after concretization.");
     check(mb200_neighbor_links_set_search_buffer(h_, buffer), "mb200_neighbor_links_set_search_buffer");
+    return *this;
+  }
+  /// Periodic box: the search, the filter and the narrow phase of collision_step() use this metric
+  /// (geom::PeriodicScaledMetric or one of the partially periodic metrics; include/mundy_b200.h
+  /// mb200_neighbor_links_set_periodic). Not a reference setter: the reference has no periodic search.
+  GenNeighborLinks& set_periodic_metric(const geom::PeriodicScaledMetric& metric) {
+    require_open("Cannot set the periodic metric after concretization.");
+    check(mb200_neighbor_links_set_periodic(h_, metric.cell_size()), "mb200_neighbor_links_set_periodic");
     return *this;
   }
   /// acts_on(source, target, generators, link parts) of the reference (:464-497) with a self-search over one body set.

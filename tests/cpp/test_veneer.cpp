@@ -173,6 +173,45 @@ int main() {
     EXPECT_TRUE(threw);
   }
 
+  // ---- periodic metrics (UnitTestPeriodicity.cpp:623-791 properties on single objects) and a periodic link build ----
+  {
+    const auto metric = geom::periodic_scaled_metric_from_unit_cell({100.0, 100.0, 100.0});
+    EXPECT_TRUE(metric.num_periodic_dimensions() == 3 && metric.is_periodic(1));
+    const geom::Vector3 d = metric.sep(Point{1, 50, 99}, Point{99, 50.5, 2});
+    EXPECT_NEAR(d[0], -2.0, 1e-12);
+    EXPECT_NEAR(d[1], 0.5, 1e-12);
+    EXPECT_NEAR(d[2], 3.0, 1e-12);
+    const Point w = metric.wrap(Point{-1, 250, 100});
+    EXPECT_NEAR(w[0], 99.0, 1e-12);
+    EXPECT_NEAR(w[1], 50.0, 1e-12);
+    EXPECT_NEAR(w[2], 0.0, 1e-12);
+    const Sphere us = geom::unwrap_points_to_ref(Sphere{Point{99, 1, 50}, 2.0}, metric, Point{101, 199, 250});
+    EXPECT_NEAR(us.center()[0], 99.0, 1e-12);
+    EXPECT_NEAR(us.center()[1], 201.0, 1e-12);
+    EXPECT_NEAR(us.center()[2], 250.0, 1e-12);
+    EXPECT_TRUE(us.radius() == 2.0);
+    const LineSegment seg = geom::unwrap_points_to_ref(LineSegment({99, 5, 5}, {2, 5, 5}), metric, Point{98, 5, 5});
+    EXPECT_NEAR(seg.end()[0] - seg.start()[0], 3.0, 1e-9);  // the spanning segment is whole again
+    const auto mx = geom::PeriodicMetricX(10.0);
+    const geom::Vector3 dx = mx.sep(Point{1, 1, 1}, Point{9, 9, 9});
+    EXPECT_NEAR(dx[0], -2.0, 1e-12);
+    EXPECT_NEAR(dx[1], 8.0, 1e-12);
+    // two spheres facing each other through the boundary: no link in free space, one link in the periodic box
+    DeviceVector<double> center(std::vector<double>{0.5, 5, 5, 9.6, 5, 5}), radius(std::vector<double>{1, 1});
+    mesh::Bodies bodies;
+    bodies.n = 2, bodies.center = center.data(), bodies.radius = radius.data();
+    mesh::GenNeighborLinks free_space, periodic;
+    free_space.set_search_buffer(0.0).acts_on(bodies).concretize();
+    periodic.set_search_buffer(0.0).set_periodic_metric(geom::periodic_scaled_metric_from_unit_cell({10.0, 10.0, 10.0}))
+        .acts_on(bodies).concretize();
+    EXPECT_TRUE(free_space.generate() && free_space.num_links() == 0);
+    EXPECT_TRUE(periodic.generate() && periodic.num_links() == 1);
+    const auto res = periodic.collision_step(1e-3, 5e-3, 1e-8, 10000);  // overlap 1.1 through the boundary is removed
+    EXPECT_TRUE(res.max_abs_projected_sep < 1e-8);
+    const auto c = center.to_host();
+    EXPECT_NEAR((c[0] + 10.0) - c[3], 2.0, 1e-7);
+  }
+
   std::printf("%d checks, %d failed\n", g_checks, g_failed);
   return g_failed == 0 ? 0 : 1;
 }
