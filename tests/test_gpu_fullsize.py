@@ -150,3 +150,36 @@ def test_cfg2_million_polydisperse_spheres_periodic(cuda):
     assert np.max(np.abs(F.sum(axis=0))) <= 1e-9 * np.abs(F).sum()
     phi1 = oracle.narrow_phase(pairs, host(c), w["radius"], cell=cell)[0]
     assert phi1.min() > -20 * tol
+
+
+def test_cfg5_jammed_mixed_packing(cuda):
+    """cfg5 at one GPU's share (5*10^5 bodies, half spheres half rods, volume fraction 0.55: dense, many contacts per
+    body, many BBPGD iterations): links exact on a sample, the contact forces are pairwise-balanced, and the state the
+    solver stops in passes the reference's own stopping test when the oracle evaluates it on the GPU's velocities."""
+    from mundy_b200 import ops
+    n = 500_000
+    w = wl.mixed(n, phi=0.55)
+    mu, dt, tol, buffer = 1e-3, 1e-4, 1e-3, 0.25
+    c, q = dev(w["center"]), dev(w["quat"])
+    b = ops.make_bodies(c, dev(w["radius"]), q, dev(w["length"]), dev(w["kind"], torch.int32))
+    links = ops.NeighborLinks().set_search_buffer(buffer).set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
+    Fcol, U, Wv = (torch.empty((n, 3), dtype=torch.float64, device="cuda") for _ in range(3))
+    c0, q0 = w["center"].copy(), w["quat"].copy()
+    st = links.step(b, mu, dt, tol, 10000, F_col=Fcol, U_out=U, W_out=Wv)
+    pairs = host(links.pairs())
+    assert st.num_links == len(pairs) > 4 * n          # jammed: more than 8 contacts per body
+    assert st.lcp.converged and st.lcp.ite_count > 100  # a hard LCP: hundreds of iterations
+    rng = np.random.default_rng(2)
+    lo = rng.uniform(0, w["edge"] - 25.0, 3)
+    inside = np.all((c0 >= lo) & (c0 <= lo + 25.0), axis=1)
+    idx = np.nonzero(inside)[0]
+    sub = oracle.search(c0[idx], oracle.search_radii(w["radius"][idx], buffer, w["kind"][idx], w["length"][idx]))
+    sub = oracle.filter_shape_distance(sub, c0[idx], q0[idx], w["radius"][idx], w["length"][idx], w["kind"][idx],
+                                       2 * buffer)
+    i, j = pairs[:, 0], pairs[:, 1]
+    assert np.array_equal(pairs[inside[i] & inside[j]], np.stack([idx[sub[:, 0]], idx[sub[:, 1]]], axis=1))
+    F = host(Fcol)
+    assert np.max(np.abs(F.sum(axis=0))) <= 1e-9 * np.abs(F).sum()
+    phi, nrm, ai, aj = oracle.narrow_phase(pairs, c0, w["radius"], q0, w["length"], w["kind"], arms=True)
+    sep = phi + dt * oracle.apply_DT(n, pairs, nrm, host(U), host(Wv), ai, aj)
+    assert sep.min() > -tol, sep.min()
