@@ -181,6 +181,21 @@ int mb200_periodic_unwrap_segments(mb200_stream stream, int64_t n, const double*
                                    const double* end, const double* ref, double* start_out, double* end_out);
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * Link data COO -> CRS. The reference keeps links in COO form (link -> linked entities,
+ * mundy/mesh/src/mundy_mesh/LinkCOOData.hpp:146-260) and rebuilds the CRS form (entity -> connected links) with
+ * NgpCOOToCRSSynchronizer (impl/NgpCOOToCRSSynchronizer.hpp:253-266: reset, gather_part_1_count with one atomic_add per
+ * linked entity :405-468, partial sum, scatter fill). Here, for links of dimensionality 2 (neighbour pairs):
+ *   linked[2 * n_links]   entity index in slot 0 / slot 1 of every link; a negative value = empty slot (skipped, :449)
+ *   offsets[n_entities+1] CRS row offsets (int64)
+ *   crs_links / crs_slots [offsets[n_entities] valid entries, capacity 2 * n_links] the links connected to each entity
+ *                         and the slot the entity occupies in them, ascending (link, slot) per entity: deterministic,
+ *                         unlike the atomic fill of the reference. crs_slots may be NULL.
+ * One stable radix sort + one scan, no floating point. Synchronises (validates the entity indices).
+ * ------------------------------------------------------------------------------------------------------------- */
+int mb200_links_coo_to_crs(mb200_stream stream, int64_t n_entities, int64_t n_links, const int32_t* linked,
+                           int64_t* offsets, int32_t* crs_links, int32_t* crs_slots);
+
+/* ---------------------------------------------------------------------------------------------------------------
  * D. Matrix-free contact operator (there is no assembled Jacobian in the reference).
  *   D   : scrap/lcp_spheres/KokkosLCP.cpp:559-591   F_i -= gamma n, F_j += gamma n ; 6-DOF scrap/UnitTestMundy.cpp:652-674
  *   M   : KokkosLCP.cpp:593-614, scrap/parameter_interface/NGPSpheresLCP.cpp:586-618 (U = F/(6 pi mu r));

@@ -100,6 +100,7 @@ SIGNATURES = {
     "mb200_periodic_wrap": (C.c_int, [vp, c_i64, P(c_dbl), vp, vp]),
     "mb200_periodic_unwrap_points": (C.c_int, [vp, c_i64, P(c_dbl), vp, vp, vp]),
     "mb200_periodic_unwrap_segments": (C.c_int, [vp, c_i64, P(c_dbl), vp, vp, vp, vp, vp]),
+    "mb200_links_coo_to_crs": (C.c_int, [vp, c_i64, c_i64, vp, vp, vp, vp]),
     "mb200_apply_D": (C.c_int, [vp, P(ContactOp), vp, vp, vp]),
     "mb200_apply_M": (C.c_int, [vp, P(ContactOp), vp, vp, vp, vp]),
     "mb200_apply_DT": (C.c_int, [vp, P(ContactOp), vp, vp, vp]),

@@ -17,6 +17,28 @@ __global__ void __launch_bounds__(256) incidence_keys_kernel(int64_t m, const in
   atomicAdd(counts + b, 1u);
 }
 
+// COO -> CRS with empty slots (entity < 0): they get the sentinel key n and sort behind every entity.
+__global__ void __launch_bounds__(256) coo_keys_kernel(int64_t m, int64_t n, const int32_t* __restrict__ linked,
+                                                       uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                                                       uint32_t* __restrict__ counts, int32_t* __restrict__ bad) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= m) return;
+  const int32_t b = linked[k];
+  if (b >= n) *bad = 1;
+  const bool empty = b < 0 || b >= n;
+  keys[k] = empty ? static_cast<uint32_t>(n) : static_cast<uint32_t>(b);
+  vals[k] = static_cast<uint32_t>(k);  // 2 * link + slot
+  if (!empty) atomicAdd(counts + b, 1u);
+}
+__global__ void __launch_bounds__(256) crs_split_kernel(int64_t m, const uint32_t* __restrict__ vals,
+                                                        int32_t* __restrict__ links, int32_t* __restrict__ slots) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= m) return;
+  const uint32_t v = vals[k];
+  links[k] = static_cast<int32_t>(v >> 1);
+  if (slots) slots[k] = static_cast<int32_t>(v & 1u);
+}
+
 template <bool SIX>
 __global__ void __launch_bounds__(128)
     apply_D_kernel(int64_t n, const int64_t* __restrict__ ptr, const uint32_t* __restrict__ list,
@@ -102,6 +124,45 @@ int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* p
 using namespace mb200;
 
 extern "C" {
+
+// the COO -> CRS synchroniser of the link data
+// (mundy/mesh/src/mundy_mesh/impl/NgpCOOToCRSSynchronizer.hpp:253-266: count with atomic_add per linked entity :405-468,
+// partial sum, scatter fill), for pair links, as one stable radix sort: deterministic, ascending (link, slot) per entity.
+int mb200_links_coo_to_crs(mb200_stream stream, int64_t n_entities, int64_t n_links, const int32_t* linked,
+                           int64_t* offsets, int32_t* crs_links, int32_t* crs_slots) {
+  MB200_REQUIRE(n_entities >= 0 && n_links >= 0 && n_entities < (int64_t(1) << 31) - 1 && n_links < (int64_t(1) << 30),
+                "bad sizes");
+  MB200_REQUIRE(offsets, "null offsets");
+  MB200_TRY(require_device());
+  cudaStream_t st = as_stream(stream);
+  const int64_t n = n_entities, m = 2 * n_links;
+  Scratch<uint32_t> counts, keys, keys_alt, vals, vals_alt;
+  Scratch<int32_t> bad;
+  MB200_TRY(counts.alloc(n > 0 ? n : 1, st));
+  MB200_TRY(bad.alloc(1, st));
+  MB200_CUDA(cudaMemsetAsync(counts.p, 0, (n > 0 ? n : 1) * sizeof(uint32_t), st));
+  MB200_CUDA(cudaMemsetAsync(bad.p, 0, sizeof(int32_t), st));
+  if (m > 0) {
+    MB200_REQUIRE(linked && crs_links, "null link arrays");
+    MB200_TRY(keys.alloc(m, st));
+    MB200_TRY(keys_alt.alloc(m, st));
+    MB200_TRY(vals.alloc(m, st));
+    MB200_TRY(vals_alt.alloc(m, st));
+    coo_keys_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, n, linked, keys.p, vals.p, counts.p, bad.p);
+    MB200_LAUNCHED();
+    int bits = 1;
+    while ((int64_t(1) << bits) < n + 1) ++bits;
+    MB200_TRY(radix_sort_u32(st, m, keys.p, keys_alt.p, vals.p, vals_alt.p, bits));
+    crs_split_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, vals.p, crs_links, crs_slots);
+    MB200_LAUNCHED();
+  }
+  MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, offsets));
+  int32_t bad_h = 0;
+  MB200_CUDA(cudaMemcpyAsync(&bad_h, bad.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  MB200_CUDA(cudaStreamSynchronize(st));
+  MB200_REQUIRE(bad_h == 0, "a link references an entity index >= n_entities");
+  return MB200_OK;
+}
 
 int mb200_apply_D(mb200_stream stream, const mb200_contact_op* op, const double* gamma, double* F, double* T) {
   MB200_TRY(check_op(op));

@@ -162,6 +162,19 @@ def search_pairs(center, search_radius, capacity=None, cell_size=None):
     return out[: count.value]
 
 
+def links_coo_to_crs(n_entities, linked):
+    """COO (n_links x 2 int32 entity indices, negative = empty slot) -> CRS: (offsets int64[n+1], links, slots)."""
+    n_links = linked.shape[0]
+    dev = linked.device
+    offsets = torch.empty(n_entities + 1, dtype=torch.int64, device=dev)
+    links = torch.empty(2 * n_links, dtype=torch.int32, device=dev)
+    slots = torch.empty(2 * n_links, dtype=torch.int32, device=dev)
+    check(lib.mb200_links_coo_to_crs(_stream(), n_entities, n_links, _i32(linked), _p(offsets), _i32(links),
+                                     _i32(slots)), "links_coo_to_crs")
+    total = int(offsets[-1].item())
+    return offsets, links[:total], slots[:total]
+
+
 class NeighborLinks:
     """mesh::GenNeighborLinks-like builder (mundy/mesh/src/mundy_mesh/GenNeighborLinkers.hpp:294-543)."""
 

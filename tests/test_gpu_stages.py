@@ -140,3 +140,32 @@ def test_narrow_phase_bit_exact(cuda, maker, kw):
     for g, x in zip(got, want):
         if x is not None:
             assert np.array_equal(host(g), x.reshape(host(g).shape))
+
+
+@pytest.mark.parametrize("n,m,empty", [(1, 0, 0.0), (50, 400, 0.0), (20000, 130001, 0.1), (7, 5000, 0.5)])
+def test_links_coo_to_crs(cuda, n, m, empty):
+    """entity -> connected links from link -> linked entities; a stable argsort in numpy is the
+    statement of the result (ascending (link, slot) per entity), the counts are the reference's atomic counts
+    (NgpCOOToCRSSynchronizer.hpp:405-468), empty slots are skipped (:449)."""
+    from mundy_b200 import ops
+    rng = np.random.default_rng(n + m)
+    linked = rng.integers(0, n, size=(m, 2)).astype(np.int32)
+    if empty > 0:
+        linked[rng.uniform(size=(m, 2)) < empty] = -1
+    off, links, slots = ops.links_coo_to_crs(n, dev(linked, torch.int32))
+    flat = linked.reshape(-1)
+    valid = np.nonzero(flat >= 0)[0]
+    order = valid[np.argsort(flat[valid], kind="stable")]
+    assert np.array_equal(host(off), np.concatenate([[0], np.cumsum(np.bincount(flat[valid], minlength=n))]))
+    assert np.array_equal(host(links), order // 2) and np.array_equal(host(slots), order % 2)
+    # every entry points back at its entity
+    o = host(off)
+    ent = np.repeat(np.arange(n), np.diff(o))
+    assert np.array_equal(linked[host(links), host(slots)], ent)
+
+
+def test_links_coo_to_crs_rejects_out_of_range(cuda):
+    from mundy_b200 import ops
+    from mundy_b200._capi import Mb200Error
+    with pytest.raises(Mb200Error):
+        ops.links_coo_to_crs(4, dev(np.array([[0, 4]]), torch.int32))
