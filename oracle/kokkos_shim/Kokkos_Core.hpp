@@ -164,5 +164,6 @@ inline void atomic_store(T* p, const U& v) {
 }  // namespace Kokkos
 
 #include "Kokkos_View_shim.hpp"
+#include "Kokkos_Team_shim.hpp"
 
 #endif  // MB200_ORACLE_KOKKOS_SHIM_CORE_HPP_

@@ -269,6 +269,71 @@ def resolve_collisions(n, pairs, normal, r, mu, dt, tol, max_it, phi0, gamma0=No
                 phi0=phi0, F=F, T=T, U=U, W=W)
 
 
+KERNEL_STOKES, KERNEL_RPY, KERNEL_RPYC, KERNEL_RPY_EXACT = 0, 1, 2, 3
+MOBILITY_LOCAL_DRAG, MOBILITY_NEIGHBORS, MOBILITY_ALL = 0, 1, 2
+
+
+def mobility_kernel(kind, mu, tpos, spos, srad, trad, sforce, tvel=None, lib=None):
+    """tvel (+)= sum over all sources of the pair kernel `kind` (Periphery.hpp apply_{stokes,rpy,rpyc}_kernel; kind 3 =
+    KokkosLCP.cpp RPYKernel). lib=oracle.ref runs the reference's own header (kinds 0-2)."""
+    tpos, spos = _a(tpos), _a(spos)
+    out = np.zeros_like(tpos) if tvel is None else _a(tvel).copy()
+    if lib is None:
+        _call(orc, "orc_mobility_kernel", int(kind), len(tpos), len(spos), float(mu), tpos, spos, _a(srad), _a(trad),
+              _a(sforce), out)
+    else:
+        rc = _call(lib, "ref_mobility_kernel", int(kind), len(tpos), len(spos), float(mu), tpos, spos, _a(srad),
+                   _a(trad), _a(sforce), out, restype=C.c_int)
+        assert rc == 0
+    return out
+
+
+def mobility_kernel_neighbors(kind, mu, pos, rad, offsets, indices, force, vel=None):
+    pos = _a(pos)
+    out = np.zeros_like(pos) if vel is None else _a(vel).copy()
+    _call(orc, "orc_mobility_kernel_neighbors", int(kind), len(pos), float(mu), pos, _a(rad), _a(offsets, _i),
+          _a(indices, _i), _a(force), out)
+    return out
+
+
+def local_drag(kind, mu, rad, force, vel=None, lib=None):
+    force = _a(force)
+    out = np.zeros_like(force) if vel is None else _a(vel).copy()
+    if lib is None:
+        _call(orc, "orc_local_drag", int(kind), len(force), float(mu), _a(rad), force, out)
+    else:
+        _call(lib, "ref_local_drag", len(force), float(mu), _a(rad), force, out, restype=C.c_int)
+    return out
+
+
+def mobility_apply(mode, kind, mu, pos, rad, F, offsets=None, indices=None):
+    pos = _a(pos)
+    U = np.empty_like(pos)
+    _call(orc, "orc_mobility_apply", int(mode), int(kind), len(pos), float(mu), pos, _a(rad), _a(offsets, _i),
+          _a(indices, _i), _a(F), U)
+    return U
+
+
+def resolve_collisions_mobility(pairs, normal, mode, kind, mu, pos, rad, dt, tol, max_it, phi0, gamma0=None,
+                                fixed_iters=-1, offsets=None, indices=None, F_ext=None):
+    """BBPGD with the mobility behind an operator (NgpHP1.cpp:1487-1645). Returns dict(res, it, max_disp, gamma, phi0, F,
+    U, U_ext)."""
+    pairs, pos = _a(pairs, _i), _a(pos)
+    n, m = len(pos), len(pairs)
+    phi0 = _a(phi0).copy()
+    gamma = np.zeros(m) if gamma0 is None else _a(gamma0).copy()
+    F, U = np.zeros((n, 3)), np.zeros((n, 3))
+    Ue = np.zeros((n, 3)) if F_ext is not None else None
+    res = CollisionResult()
+    fn = orc.orc_resolve_collisions_mobility
+    fn.restype = None
+    fn(C.c_long(n), C.c_long(m), _p(pairs), _p(_a(normal)), C.c_int(mode), C.c_int(kind), C.c_double(mu), _p(pos),
+       _p(_a(rad)), _p(_a(offsets, _i)), _p(_a(indices, _i)), C.c_double(dt), C.c_double(tol), C.c_int(max_it),
+       C.c_int(fixed_iters), _p(_a(F_ext)), _p(Ue), _p(phi0), _p(gamma), _p(F), _p(U), C.byref(res))
+    return dict(res=res.max_abs_projected_sep, it=res.ite_count, max_disp=res.max_displacement, gamma=gamma, phi0=phi0,
+                F=F, U=U, U_ext=Ue)
+
+
 def euler_update(pos, U, dt, quat=None, kind=None, W=None):
     pos = _a(pos).copy()
     q = _a(quat).copy() if quat is not None else None
