@@ -292,6 +292,63 @@ int mb200_solve_lcp_contact(mb200_stream stream, const mb200_contact_op* op, con
                             const mb200_pgd_config* cfg, mb200_solve_result* result_h);
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * G. Non-local mobility operators behind `ApplyMobilityOp`. Spheres, translational part.
+ *   pair kernels  scrap/parameter_interface/alens/src/mundy_alens/periphery/Periphery.hpp: apply_stokes_kernel :686-747,
+ *                 apply_rpy_kernel :847-942 (quake_inv_sqrt :72-82), apply_rpyc_kernel :954-1085, apply_local_drag
+ *                 :1316-1354; scrap/lcp_spheres/KokkosLCP.cpp: RPYKernel :219-280 (one radius, 1/sqrt),
+ *                 apply_rpy_kernel_neighbors :305-333, compute_the_mobility_problem :593-614
+ *   operator      scrap/parameter_interface/alens/tests/performance_tests/NgpHP1.cpp: compute_rpy_mobility_spheres :677-701,
+ *                 SphereLocalDragMobilityOp / SphereRpyMobilityOp :804-925
+ *   solve         NgpHP1.cpp resolve_collisions<ApplyMobilityOp> :1487-1645
+ * The sum over the sources of one target is taken in ascending source (CSR row) order from zero, then added to the
+ * target velocity: deterministic, and bit-identical to the reference's kernels on the Kokkos Serial backend.
+ * ------------------------------------------------------------------------------------------------------------- */
+enum mb200_mobility_kernel {
+  MB200_KERNEL_STOKES = 0,    /* Periphery.hpp apply_stokes_kernel (radii unused, may be NULL) */
+  MB200_KERNEL_RPY = 1,       /* Periphery.hpp apply_rpy_kernel: a = source radius, b = target radius, quake_inv_sqrt */
+  MB200_KERNEL_RPYC = 2,      /* Periphery.hpp apply_rpyc_kernel: overlap-corrected RPY */
+  MB200_KERNEL_RPY_EXACT = 3  /* KokkosLCP.cpp RPYKernel: 1/sqrt, radius taken from the source, self term 1/(6 pi r mu) */
+};
+enum mb200_mobility_mode {
+  MB200_MOBILITY_LOCAL_DRAG = 0, /* U = F / (6 pi mu r)                                  (HydroType DRY)           */
+  MB200_MOBILITY_NEIGHBORS = 1,  /* + pair kernel over the sources of a CSR neighbour list (HYDRO_NEAREST / DISTANT) */
+  MB200_MOBILITY_ALL = 2         /* + pair kernel over all spheres                         (HYDRO_ALL)               */
+};
+/* target_vel[3 nt] += sum over ALL ns sources of K(target, source) source_force. Self pairs (r^2 < 1e-12) add nothing.
+ * source_radii / target_radii may be NULL for MB200_KERNEL_STOKES. */
+int mb200_mobility_kernel_apply(mb200_stream stream, int kernel, int64_t nt, int64_t ns, double viscosity,
+                                const double* target_pos, const double* source_pos, const double* source_radii,
+                                const double* target_radii, const double* source_force, double* target_vel);
+/* vel[3n] += sum over the sources indices[offsets[t] .. offsets[t+1]) of each target t (sources == targets). */
+int mb200_mobility_kernel_apply_neighbors(mb200_stream stream, int kernel, int64_t n, double viscosity,
+                                          const double* pos, const double* radii, const int32_t* offsets,
+                                          const int32_t* indices, const double* force, double* vel);
+/* vel[3n] += force / (6 pi mu r): apply_local_drag (kernel selects which of the two reference forms of the coefficient). */
+int mb200_apply_local_drag(mb200_stream stream, int kernel, int64_t n, double viscosity, const double* radii,
+                           const double* force, double* vel);
+
+typedef struct mb200_mobility_op { /* the state an `ApplyMobilityOp` holds (NgpHP1.cpp:833-925) */
+  int64_t n;
+  int32_t mode;               /* mb200_mobility_mode */
+  int32_t kernel;             /* mb200_mobility_kernel */
+  double viscosity;
+  const double* pos;          /* [3n] (unused for LOCAL_DRAG) */
+  const double* radius;       /* [n] */
+  const int32_t* nbr_offsets; /* [n+1] (NEIGHBORS) */
+  const int32_t* nbr_indices;
+} mb200_mobility_op;
+/* U[3n] = M F: zero, non-local kernel, local drag (`apply(force, velocity)` of the operator). */
+int mb200_mobility_apply(mb200_stream stream, const mb200_mobility_op* mob, const double* F, double* U);
+
+/* BBPGD with U = M F delegated to the operator. op: 3-DOF contact operator (arm_i = arm_j = NULL; its radius / viscosity
+ * are not used). F_ext[3n] != NULL: U_ext = M F_ext is written to U_ext_out (nullable) and phi0 += dt D^T U_ext.
+ * phi0, gamma in/out; F, U out (collision force and velocity). result_h is a HOST struct; synchronises. */
+int mb200_resolve_collisions_mobility(mb200_stream stream, const mb200_contact_op* op, const mb200_mobility_op* mob,
+                                      const mb200_lcp_params* params, const double* F_ext, double* U_ext_out,
+                                      double* phi0, double* gamma, double* F, double* U,
+                                      mb200_collision_result* result_h);
+
+/* ---------------------------------------------------------------------------------------------------------------
  * E3. Euler update  x += dt U (KokkosLCP.cpp:1015); rods: q <- math::rotate_quaternion(q, W, dt)
  * (mundy/math/src/mundy_math/Quaternion.hpp:1359-1385). quat/kind/W may be NULL.
  * ------------------------------------------------------------------------------------------------------------- */

@@ -52,6 +52,11 @@ class SolveResult(C.Structure):
     _fields_ = [("num_iters", C.c_uint32), ("residual", c_dbl), ("converged", c_i32)]
 
 
+class MobilityOp(C.Structure):
+    _fields_ = [("n", c_i64), ("mode", c_i32), ("kernel", c_i32), ("viscosity", c_dbl), ("pos", vp), ("radius", vp),
+                ("nbr_offsets", vp), ("nbr_indices", vp)]
+
+
 class StepParams(C.Structure):
     _fields_ = [("viscosity", c_dbl), ("dt", c_dbl), ("tol", c_dbl), ("max_iters", c_i32), ("fixed_iters", c_i32),
                 ("throw_on_max_iters", c_i32), ("force_rebuild", c_i32)]
@@ -107,6 +112,12 @@ SIGNATURES = {
     "mb200_apply_A": (C.c_int, [vp, P(ContactOp), vp, vp]),
     "mb200_resolve_collisions": (C.c_int, [vp, P(ContactOp), P(LcpParams), vp, vp, vp, vp, vp, vp, vp, vp,
                                            P(CollisionResult)]),
+    "mb200_mobility_kernel_apply": (C.c_int, [vp, C.c_int, c_i64, c_i64, c_dbl, vp, vp, vp, vp, vp, vp]),
+    "mb200_mobility_kernel_apply_neighbors": (C.c_int, [vp, C.c_int, c_i64, c_dbl, vp, vp, vp, vp, vp, vp]),
+    "mb200_apply_local_drag": (C.c_int, [vp, C.c_int, c_i64, c_dbl, vp, vp, vp]),
+    "mb200_mobility_apply": (C.c_int, [vp, P(MobilityOp), vp, vp]),
+    "mb200_resolve_collisions_mobility": (C.c_int, [vp, P(ContactOp), P(MobilityOp), P(LcpParams), vp, vp, vp, vp, vp,
+                                                    vp, P(CollisionResult)]),
     "mb200_vec_axpby": (C.c_int, [vp, c_i64, c_dbl, vp, c_dbl, vp]),
     "mb200_vec_wrapped_axpbyz": (C.c_int, [vp, c_i64, c_dbl, vp, c_dbl, vp, vp, C.c_int, c_dbl, c_dbl]),
     "mb200_vec_diff_dot": (C.c_int, [vp, c_i64, vp, vp, P(c_dbl)]),

@@ -297,6 +297,59 @@ def resolve_collisions(op, phi0, gamma, tol, max_iters, fixed_iters=-1, U_ext=No
     return res, F, T, U, W
 
 
+# G. non-local mobility operators ---------------------------------------------------------------
+KERNEL_STOKES, KERNEL_RPY, KERNEL_RPYC, KERNEL_RPY_EXACT = 0, 1, 2, 3
+MOBILITY_LOCAL_DRAG, MOBILITY_NEIGHBORS, MOBILITY_ALL = 0, 1, 2
+
+
+def mobility_kernel_apply(kernel, viscosity, target_pos, source_pos, source_radii, target_radii, source_force,
+                          target_vel):
+    """target_vel += sum over all sources (in place)."""
+    check(lib.mb200_mobility_kernel_apply(_stream(), kernel, target_pos.shape[0], source_pos.shape[0], viscosity,
+                                          _f64(target_pos), _f64(source_pos), _f64(source_radii), _f64(target_radii),
+                                          _f64(source_force), _f64(target_vel)), "mobility_kernel_apply")
+    return target_vel
+
+
+def mobility_kernel_apply_neighbors(kernel, viscosity, pos, radii, offsets, indices, force, vel):
+    check(lib.mb200_mobility_kernel_apply_neighbors(_stream(), kernel, pos.shape[0], viscosity, _f64(pos), _f64(radii),
+                                                    _i32(offsets), _i32(indices), _f64(force), _f64(vel)),
+          "mobility_kernel_apply_neighbors")
+    return vel
+
+
+def apply_local_drag(kernel, viscosity, radii, force, vel):
+    check(lib.mb200_apply_local_drag(_stream(), kernel, radii.numel(), viscosity, _f64(radii), _f64(force), _f64(vel)),
+          "apply_local_drag")
+    return vel
+
+
+def make_mobility_op(mode, kernel, viscosity, radius, pos=None, offsets=None, indices=None):
+    op = capi.MobilityOp(radius.numel(), mode, kernel, viscosity, _f64(pos), _f64(radius), _i32(offsets), _i32(indices))
+    op._keep = (pos, radius, offsets, indices)
+    return op
+
+
+def mobility_apply(mob, F):
+    U = torch.empty_like(F)
+    check(lib.mb200_mobility_apply(_stream(), C.byref(mob), _f64(F), _f64(U)), "mobility_apply")
+    return U
+
+
+def resolve_collisions_mobility(op, mob, phi0, gamma, tol, max_iters, fixed_iters=-1, F_ext=None):
+    """phi0 and gamma are updated in place. Returns (result, F, U, U_ext)."""
+    dev = phi0.device
+    F = torch.empty((op.n, 3), dtype=torch.float64, device=dev)
+    U = torch.empty((op.n, 3), dtype=torch.float64, device=dev)
+    Ue = torch.empty((op.n, 3), dtype=torch.float64, device=dev) if F_ext is not None else None
+    params = capi.LcpParams(tol, max_iters, fixed_iters)
+    res = capi.CollisionResult()
+    check(lib.mb200_resolve_collisions_mobility(_stream(), C.byref(op), C.byref(mob), C.byref(params), _f64(F_ext),
+                                                _f64(Ue), _f64(phi0), _f64(gamma), _f64(F), _f64(U), C.byref(res)),
+          "resolve_collisions_mobility")
+    return res, F, U, Ue
+
+
 def solve_cqpp_dense(A, q, x, max_iters=1000, tol=1e-8, space_kind=1, lo=0.0, hi=0.0, residual_kind=0):
     cfg = capi.PgdConfig(max_iters, tol, space_kind, lo, hi, residual_kind)
     res = capi.SolveResult()

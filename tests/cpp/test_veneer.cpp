@@ -10,6 +10,7 @@
 
 #include "mundy_b200/convex.hpp"
 #include "mundy_b200/geom.hpp"
+#include "mundy_b200/mobility.hpp"
 #include "mundy_b200/neighbor_links.hpp"
 
 using namespace mundy_b200;
@@ -210,6 +211,58 @@ int main() {
     EXPECT_TRUE(res.max_abs_projected_sep < 1e-8);
     const auto c = center.to_host();
     EXPECT_NEAR((c[0] + 10.0) - c[3], 2.0, 1e-7);
+  }
+
+  // ---- mobility operators (UnitTestPeriphery.cpp:671-775 three spheres; NgpHP1.cpp:1487-1645 solve) ----
+  {
+    namespace per = alens::periphery;
+    const double radius = 12.34, s = 6.0, pi = 3.14159265358979323846;
+    const std::vector<double> pos{0, 0, 0, -s * radius / 2, -std::sqrt(3.0) * s * radius / 2, 0,
+                                  s * radius / 2, -std::sqrt(3.0) * s * radius / 2, 0};
+    std::vector<double> f(9, 0.0);
+    f[1] = -6.0 * pi * radius;
+    DeviceVector<double> positions(pos), radii(std::vector<double>(3, radius)), forces(f);
+    DeviceVector<double> v_rpy(std::vector<double>(9, 0.0)), v_rpyc(std::vector<double>(9, 0.0));
+    per::apply_rpy_kernel(per::DeviceSpace{}, 1.0, positions, positions, radii, radii, forces, v_rpy);
+    per::apply_rpyc_kernel(per::DeviceSpace{}, 1.0, positions, positions, radii, radii, forces, v_rpyc);
+    per::apply_local_drag(per::DeviceSpace{}, 1.0, v_rpy, forces, radii);  // "add self-interaction"
+    per::apply_local_drag(per::DeviceSpace{}, 1.0, v_rpyc, forces, radii);
+    const auto a = v_rpy.to_host(), b = v_rpyc.to_host();
+    EXPECT_NEAR(-a[1], 1.0, 1e-12);         // U1
+    EXPECT_NEAR(-a[4], 0.21586, 1e-3);      // U2 (Wilson 2013, s = 6)
+    EXPECT_NEAR(a[6], 0.05078, 1e-3);       // U3
+    EXPECT_NEAR(-b[4], 0.21586, 1e-4);
+    bool threw = false;
+    try {
+      DeviceVector<double> short_forces(std::vector<double>(6, 0.0));
+      per::apply_rpy_kernel(per::DeviceSpace{}, 1.0, positions, positions, radii, radii, short_forces, v_rpy);
+    } catch (const std::invalid_argument&) {
+      threw = true;
+    }
+    EXPECT_TRUE(threw);
+    // the operator assigns: velocity = M force, whatever velocity held
+    alens::SphereRpyMobilityOp rpy_op(1.0, positions, radii, MB200_KERNEL_RPYC);
+    DeviceVector<double> u(std::vector<double>(9, 123.0));
+    rpy_op.update();
+    rpy_op.apply(forces, u);
+    const auto uh = u.to_host();
+    for (int k = 0; k < 9; ++k) EXPECT_NEAR(uh[k], b[k], 1e-15);
+    // two overlapping spheres pushed apart with hydrodynamic coupling: the overlap is removed, both move (Newton pair)
+    DeviceVector<double> p2(std::vector<double>{0, 0, 0, 1.5, 0, 0}), r2(std::vector<double>{1.0, 1.0});
+    DeviceVector<int32_t> ids(std::vector<int32_t>{0, 1});
+    DeviceVector<double> sep(std::vector<double>{-0.5}), nrm(std::vector<double>{1, 0, 0}), gam(std::vector<double>{0.0});
+    DeviceVector<double> cf(std::vector<double>(6, 0.0)), cu(std::vector<double>(6, 0.0));
+    alens::SphereRpyMobilityOp op2(1e-3, p2, r2, MB200_KERNEL_RPYC);
+    const auto res = alens::resolve_collisions(1e-2, 1e-10, 1000, op2, ids, nullptr, nullptr, cf, cu, sep, nrm, gam);
+    EXPECT_TRUE(res.max_abs_projected_sep < 1e-10 && res.ite_count >= 1);
+    const auto uu = cu.to_host();
+    EXPECT_NEAR(uu[3] - uu[0], 0.5 / 1e-2, 1e-6);  // relative normal velocity closes the overlap in one step
+    EXPECT_NEAR(uu[0] + uu[3], 0.0, 1e-9);
+    alens::SphereLocalDragMobilityOp dry(1e-3, r2);
+    DeviceVector<double> gam2(std::vector<double>{0.0}), sep2(std::vector<double>{-0.5});
+    const auto res_dry = alens::resolve_collisions(1e-2, 1e-10, 1000, dry, ids, nullptr, nullptr, cf, cu, sep2, nrm, gam2);
+    EXPECT_TRUE(res_dry.max_abs_projected_sep < 1e-10);
+    EXPECT_TRUE(gam2.to_host()[0] < gam.to_host()[0]);  // the coupling drags the partner along: more force is needed
   }
 
   std::printf("%d checks, %d failed\n", g_checks, g_failed);
