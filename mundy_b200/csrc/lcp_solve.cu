@@ -47,6 +47,10 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
   const D4* mob;      // [n] mobility records
   const int64_t* inc_ptr;
   const uint32_t* inc_list;
+  // entry-major mirror of the static contact data (built once per solve, after the phi0 correction): for incidence
+  // entry k = (contact c, side s): ent0[k] = {n_s, phi0_c}, n_s = +/- n; ent1[k] = {r_s x n_s, -} (6-DOF only)
+  const D4* ent0;
+  const D4* ent1;
   D4* vel;  // [n] (3-DOF) or [2n] (6-DOF)
   double mu, dt, tol;
   int32_t fixed;   // ignore tol
@@ -214,6 +218,26 @@ __device__ inline void cp_async8(void* smem_dst, const void* gsrc) {
 }
 __device__ inline void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// Static per-entry data in incidence order, so that the body pass streams it (two coalesced 256-bit loads per entry)
+// and only the 16-byte state of the contact is gathered.
+template <bool SIX>
+__global__ void __launch_bounds__(256) entry_mirror_kernel(int64_t m, int64_t npairs, const uint32_t* __restrict__ list,
+                                                           const D4* __restrict__ rec, D4* __restrict__ ent0,
+                                                           D4* __restrict__ ent1) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= m) return;
+  const uint32_t e = __ldg(list + k);
+  const int64_t c = e >> 1;
+  const bool is_j = e & 1u;
+  const D4 r0 = ldg256(rec + c);
+  const double mx = is_j ? -r0.x : r0.x, my = is_j ? -r0.y : r0.y, mz = is_j ? -r0.z : r0.z;
+  st256(ent0 + k, D4{mx, my, mz, r0.w});
+  if (SIX) {
+    const D4 ra = ldg256(rec + (is_j ? 2 : 1) * npairs + c);
+    st256(ent1 + k, D4{ra.y * mz - ra.z * my, ra.z * mx - ra.x * mz, ra.x * my - ra.y * mx, 0.0});
+  }
+}
+
 // End of a body's pass: U = M F from the summed wrench; velocity records (and, multi-GPU, their ghost copies on the
 // peers) or, in the FINAL pass, the solver's outputs.
 template <bool SIX, bool FINAL>
@@ -350,27 +374,25 @@ __global__ void __launch_bounds__(kBodyThreads)
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
           if (e[u] != 0xffffffffu) {
-            const int64_t c = e[u] >> 1;
-            sp[u] = ldg128(st_prev + c);
-            r0[u] = ldg256(a.rec + c);
-            if (SIX) ra[u] = ldg256(a.rec + (1 + (e[u] & 1u)) * a.npairs + c);
+            const int64_t k = rb + k0 + u * kBodyThreads + t;
+            sp[u] = ldg128(st_prev + (e[u] >> 1));  // the only gather: 16 bytes of state per entry
+            r0[u] = ldg256(a.ent0 + k);             // streamed
+            if (SIX) ra[u] = ldg256(a.ent1 + k);
           }
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
           if (e[u] != 0xffffffffu) {
             const int k = k0 + u * kBodyThreads + t;
-            const int is_j = e[u] & 1u;
             const double g = gamma_of<MODE>(sp[u], r0[u].w, alpha, a.dt, first);
             // n_I = n, n_J = -n: F += -gamma n_side, T += -gamma (r_side x n_side)  (scrap/UnitTestMundy.cpp:652-674)
-            const double mx = is_j ? -r0[u].x : r0[u].x, my = is_j ? -r0[u].y : r0[u].y, mz = is_j ? -r0[u].z : r0[u].z;
-            s_w[0][k] = -g * mx;
-            s_w[1][k] = -g * my;
-            s_w[2][k] = -g * mz;
+            s_w[0][k] = -g * r0[u].x;
+            s_w[1][k] = -g * r0[u].y;
+            s_w[2][k] = -g * r0[u].z;
             if (SIX) {
-              s_w[3][k] = -g * (ra[u].y * mz - ra[u].z * my);
-              s_w[4][k] = -g * (ra[u].z * mx - ra[u].x * mz);
-              s_w[5][k] = -g * (ra[u].x * my - ra[u].y * mx);
+              s_w[3][k] = -g * ra[u].x;
+              s_w[4][k] = -g * ra[u].y;
+              s_w[5][k] = -g * ra[u].z;
             }
           }
         }
@@ -657,6 +679,11 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   Scratch<double2> s0, s1;
   Scratch<D4> vel, mob;
   Scratch<LcpState> state;
+  // The entry mirrors are the largest buffers of the solve (128 B per contact): kept per host thread and only ever
+  // grown, so that a step does not carve them out of (and fragment) the stream-ordered pool every time.
+  static thread_local DevBuf<D4> ent0, ent1;
+  MB200_TRY(ent0.reserve(2 * C > 0 ? 2 * C : 1));
+  if (six) MB200_TRY(ent1.reserve(2 * C > 0 ? 2 * C : 1));
   MB200_TRY(s0.alloc(C, st));
   MB200_TRY(s1.alloc(C, st));
   MB200_TRY(partials.alloc(4 * static_cast<size_t>(rate_grid), st));
@@ -670,6 +697,7 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   a.n = n, a.npairs = C;
   a.pairs = sys.pairs, a.rec = sys.rec, a.mob = mob.p;
   a.inc_ptr = inc.ptr.p, a.inc_list = inc.list.p;
+  a.ent0 = ent0.p, a.ent1 = ent1.p;
   a.vel = peer_mode ? dist->vel_arena : vel.p;
   a.peer = peer_mode ? dist->peer_dev : nullptr;
   a.halo_seq = 0, a.red_seq = 0;
@@ -747,6 +775,13 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
         ext_correction_kernel<true><<<cgrid, 256, 0, st>>>(C, sys.pairs, sys.rec, U_ext, W_ext, a.dt);
       else
         ext_correction_kernel<false><<<cgrid, 256, 0, st>>>(C, sys.pairs, sys.rec, U_ext, nullptr, a.dt);
+      MB200_LAUNCHED();
+    }
+    if (C > 0) {
+      if (six)
+        entry_mirror_kernel<true><<<grid_for(2 * C, 256), 256, 0, st>>>(2 * C, C, inc.list.p, sys.rec, ent0.p, ent1.p);
+      else
+        entry_mirror_kernel<false><<<grid_for(2 * C, 256), 256, 0, st>>>(2 * C, C, inc.list.p, sys.rec, ent0.p, nullptr);
       MB200_LAUNCHED();
     }
   }

@@ -25,7 +25,7 @@ namespace {
 
 constexpr double kDoubleZero = 1e-12;  // DOUBLE_ZERO (Periphery.hpp:67, KokkosLCP.cpp:34)
 constexpr double kPi = 3.14159265358979323846;
-constexpr int kTargets = 128;  // targets (threads) per CTA
+constexpr int kTargets = 64;   // targets (threads) per CTA: 65 536 targets = 1024 CTAs, 6.9 per SM (128 left a 4-vs-3 imbalance)
 constexpr int kTileSrc = 256;  // sources staged per round: 16 KB
 
 // Periphery.hpp:72-82: bit trick + one Newton iteration; it is the reference's arithmetic, error ~1.7e-3 included.
