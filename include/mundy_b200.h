@@ -93,6 +93,48 @@ int mb200_distance_segment_sphere(mb200_stream stream, int64_t n, const double* 
                                   const double* r, double* dist, double* t, double* cp, double* sep);
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * A'/C'. The remaining primitives of mundy_geom, batched like the sections above.
+ *    quat[4n] = (w,x,y,z), not assumed unit-norm; radii[3n] = the three semi-axes in the body frame; a Line is
+ *    (center[3n], direction[3n]). Output pointers other than aabb may be NULL.
+ * ------------------------------------------------------------------------------------------------------------- */
+/* compute_aabb(Point)  mundy/geom/src/mundy_geom/compute_aabb.hpp:47-54 */
+int mb200_compute_aabb_point(mb200_stream stream, int64_t n, const double* point, double* aabb);
+/* compute_aabb(LineSegment)  compute_aabb.hpp:57-69 */
+int mb200_compute_aabb_line_segment(mb200_stream stream, int64_t n, const double* start, const double* end,
+                                    double* aabb);
+/* compute_aabb(Ellipsoid)  compute_aabb.hpp:83-103: corners center -/+ (orientation * radii), per-axis min / max */
+int mb200_compute_aabb_ellipsoid(mb200_stream stream, int64_t n, const double* center, const double* quat,
+                                 const double* radii, double* aabb);
+/* distance(Point, Sphere, sep)  distance/PointSphere.hpp:68-76 */
+int mb200_distance_point_sphere(mb200_stream stream, int64_t n, const double* x, const double* c, const double* r,
+                                double* dist, double* sep);
+/* distance(Point, Line, cp, arch_length, sep)  distance/PointLine.hpp:92-103 (the reference leaves sep unwritten) */
+int mb200_distance_point_line(mb200_stream stream, int64_t n, const double* x, const double* line_center,
+                              const double* line_dir, double* dist, double* cp, double* arch);
+/* distance(Line, Line, cp1, cp2, arch1, arch2, sep)  distance/LineLine.hpp:131-157. Parallel lines (D < 1e-15): the
+ * reference returns 0 with sep = 0 and leaves cp/arch untouched; here those outputs are written as 0. */
+int mb200_distance_line_line(mb200_stream stream, int64_t n, const double* c1, const double* d1, const double* c2,
+                             const double* d2, double* dist, double* cp1, double* cp2, double* arch1, double* arch2,
+                             double* sep);
+/* distance(Line, Sphere, cp, arch_length, sep)  distance/LineSphere.hpp:93-102 */
+int mb200_distance_line_sphere(mb200_stream stream, int64_t n, const double* line_center, const double* line_dir,
+                               const double* c, const double* r, double* dist, double* cp, double* arch);
+/* distance(SharedNormalSigned, Point, Ellipsoid, closest_point, ellipsoid_normal)  distance/PointEllipsoid.hpp:97-135.
+ * Found by math::find_min_using_approximate_derivatives (mundy/math/src/mundy_math/minimize.hpp:41-50: L-BFGS memory
+ * 10, central differences, Wolfe line search) over the normal's two angles from nine starts, like the next two. */
+int mb200_distance_point_ellipsoid(mb200_stream stream, int64_t n, const double* x, const double* center,
+                                   const double* quat, const double* radii, double* dist, double* cp, double* normal);
+/* distance(SharedNormalSigned, Ellipsoid, Ellipsoid, cp1, cp2, normal1, normal2)  distance/EllipsoidEllipsoid.hpp:109-151
+ * (normal2 = -normal1 is not stored) */
+int mb200_distance_ellipsoid_ellipsoid(mb200_stream stream, int64_t n, const double* c1, const double* q1,
+                                       const double* radii1, const double* c2, const double* q2,
+                                       const double* radii2, double* dist, double* cp1, double* cp2, double* normal1);
+/* distance(Euclidean, Circle3D, Circle3D, cp1, cp2, normal1, normal2)  distance/Circle3DCircle3D.hpp:88-151 */
+int mb200_distance_circle3d_circle3d(mb200_stream stream, int64_t n, const double* c1, const double* q1,
+                                     const double* r1, const double* c2, const double* q2, const double* r2,
+                                     double* dist, double* cp1, double* cp2, double* normal1);
+
+/* ---------------------------------------------------------------------------------------------------------------
  * Body set in the caller's (reference) layout. kind/quat/length may be NULL when every body is a sphere.
  * ------------------------------------------------------------------------------------------------------------- */
 typedef struct mb200_bodies {

@@ -89,6 +89,16 @@ SIGNATURES = {
     "mb200_distance_segment_segment": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "mb200_distance_point_segment": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp]),
     "mb200_distance_segment_sphere": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "mb200_compute_aabb_point": (C.c_int, [vp, c_i64, vp, vp]),
+    "mb200_compute_aabb_line_segment": (C.c_int, [vp, c_i64, vp, vp, vp]),
+    "mb200_compute_aabb_ellipsoid": (C.c_int, [vp, c_i64, vp, vp, vp, vp]),
+    "mb200_distance_point_sphere": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp]),
+    "mb200_distance_point_line": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp]),
+    "mb200_distance_line_line": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "mb200_distance_line_sphere": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp]),
+    "mb200_distance_point_ellipsoid": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp]),
+    "mb200_distance_ellipsoid_ellipsoid": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "mb200_distance_circle3d_circle3d": (C.c_int, [vp, c_i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "mb200_narrow_phase": (C.c_int, [vp, P(Bodies), c_i64, vp, vp, vp, vp, vp]),
     "mb200_neighbor_links_create": (C.c_int, [P(vp)]),
     "mb200_neighbor_links_destroy": (C.c_int, [vp]),

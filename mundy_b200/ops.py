@@ -100,6 +100,60 @@ def distance_segment_sphere(p1, p2, c, r):
     return dist, t, cp, sep
 
 
+# ---- the remaining primitives; argument order = the C-ABI's ------------------------------------
+def _prim(name, n, like, inputs, widths):
+    outs = [_new(n if w == 1 else (n, w), like) for w in widths]
+    check(getattr(lib, "mb200_" + name)(_stream(), n, *[_f64(x) for x in inputs], *[_f64(o) for o in outs]), name)
+    return outs[0] if len(outs) == 1 else tuple(outs)
+
+
+def compute_aabb_point(point):
+    return _prim("compute_aabb_point", point.shape[0], point, (point,), (6,))
+
+
+def compute_aabb_line_segment(start, end):
+    return _prim("compute_aabb_line_segment", start.shape[0], start, (start, end), (6,))
+
+
+def compute_aabb_ellipsoid(center, quat, radii):
+    return _prim("compute_aabb_ellipsoid", center.shape[0], center, (center, quat, radii), (6,))
+
+
+def distance_point_sphere(x, c, r):
+    """-> dist, sep"""
+    return _prim("distance_point_sphere", x.shape[0], x, (x, c, r), (1, 3))
+
+
+def distance_point_line(x, line_center, line_dir):
+    """-> dist, closest point, arch length"""
+    return _prim("distance_point_line", x.shape[0], x, (x, line_center, line_dir), (1, 3, 1))
+
+
+def distance_line_line(c1, d1, c2, d2):
+    """-> dist, cp1, cp2, arch1, arch2, sep"""
+    return _prim("distance_line_line", c1.shape[0], c1, (c1, d1, c2, d2), (1, 3, 3, 1, 1, 3))
+
+
+def distance_line_sphere(line_center, line_dir, c, r):
+    """-> dist, closest point on the line, arch length"""
+    return _prim("distance_line_sphere", c.shape[0], c, (line_center, line_dir, c, r), (1, 3, 1))
+
+
+def distance_point_ellipsoid(x, center, quat, radii):
+    """-> signed distance, closest point on the ellipsoid, ellipsoid normal there"""
+    return _prim("distance_point_ellipsoid", x.shape[0], x, (x, center, quat, radii), (1, 3, 3))
+
+
+def distance_ellipsoid_ellipsoid(c1, q1, radii1, c2, q2, radii2):
+    """-> shared-normal signed distance, cp1, cp2, shared normal of the first"""
+    return _prim("distance_ellipsoid_ellipsoid", c1.shape[0], c1, (c1, q1, radii1, c2, q2, radii2), (1, 3, 3, 3))
+
+
+def distance_circle3d_circle3d(c1, q1, r1, c2, q2, r2):
+    """-> Euclidean distance, cp1, cp2, unit vector from cp1 to cp2"""
+    return _prim("distance_circle3d_circle3d", c1.shape[0], c1, (c1, q1, r1, c2, q2, r2), (1, 3, 3, 3))
+
+
 # ---------------------------------------------------------------------------------------------------------------
 def make_bodies(center, radius, quat=None, length=None, kind=None):
     b = capi.Bodies(radius.numel(), _f64(center), _f64(quat), _f64(radius), _f64(length), _i32(kind))

@@ -304,3 +304,4 @@ void orc_seg_sphere(long n, const double* p1, const double* p2, const double* c,
 #include "mundy_oracle_collision.inc"
 #include "mundy_oracle_convex.inc"
 #include "mundy_oracle_mobility.inc"
+#include "mundy_oracle_primitives.inc"

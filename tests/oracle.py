@@ -100,6 +100,29 @@ def rotate_quaternion(quat, omega, dt, lib=None, prefix="orc_"):
     return q
 
 
+# ---- remaining primitives: one generic front-end, outputs shaped by PRIMITIVE_OUTPUTS ------------
+# name -> per-item widths of the output arrays, in call order
+PRIMITIVE_OUTPUTS = {
+    "aabb_point": (6,), "aabb_line_segment": (6,), "aabb_ellipsoid": (6,),
+    "point_sphere": (1, 3),                    # dist, sep
+    "point_line": (1, 3, 1),                   # dist, closest point, arch length
+    "line_line": (1, 3, 3, 1, 1, 3),           # dist, cp1, cp2, arch1, arch2, sep
+    "line_sphere": (1, 3, 1),                  # dist, closest point, arch length
+    "point_ellipsoid": (1, 3, 3),              # dist, closest point, ellipsoid normal
+    "ellipsoid_ellipsoid": (1, 3, 3, 3),       # dist, cp1, cp2, shared normal of the first
+    "circle_circle": (1, 3, 3, 3),             # dist, cp1, cp2, unit vector from cp1 to cp2
+}
+
+
+def primitive(name, *inputs, lib=None, prefix="orc_"):
+    lib = lib or orc
+    ins = [_a(x) for x in inputs]
+    n = len(ins[0])
+    outs = [np.zeros(n) if w == 1 else np.zeros((n, w)) for w in PRIMITIVE_OUTPUTS[name]]
+    _call(lib, prefix + name, n, *ins, *outs)
+    return outs[0] if len(outs) == 1 else tuple(outs)
+
+
 def segseg(l0, l1, m0, m1, lib=None, prefix="orc_"):
     lib = lib or orc
     l0, l1, m0, m1 = _a(l0), _a(l1), _a(m0), _a(m1)
