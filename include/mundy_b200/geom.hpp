@@ -113,6 +113,43 @@ class SpherocylinderSegment {
   double r_;
 };
 
+class Line {  // primitives/Line.hpp: a point on the line and its direction (not assumed unit)
+ public:
+  Line(const Point& c, const Vector3& d) : c_(c), d_(d) {}
+  const Point& center() const { return c_; }
+  const Vector3& direction() const { return d_; }
+
+ private:
+  Point c_;
+  Vector3 d_;
+};
+class Ellipsoid {  // primitives/Ellipsoid.hpp:130-143: centre, orientation, three body-frame semi-axes
+ public:
+  Ellipsoid(const Point& c, const Quaternion& q, const Vector3& radii) : c_(c), q_(q), r_(radii) {}
+  Ellipsoid(const Point& c, const Quaternion& q, double r1, double r2, double r3) : c_(c), q_(q), r_(r1, r2, r3) {}
+  const Point& center() const { return c_; }
+  const Quaternion& orientation() const { return q_; }
+  const Vector3& radii() const { return r_; }
+
+ private:
+  Point c_;
+  Quaternion q_;
+  Vector3 r_;
+};
+class Circle3D {  // primitives/Circle3D.hpp:98-110: the circle lies in the body-frame xy plane
+ public:
+  Circle3D(const Point& c, const Quaternion& q, double r) : c_(c), q_(q), r_(r) {}
+  const Point& center() const { return c_; }
+  const Quaternion& orientation() const { return q_; }
+  double radius() const { return r_; }
+
+ private:
+  Point c_;
+  Quaternion q_;
+  double r_;
+};
+struct Euclidean {};  // distance/Types.hpp
+
 // ---- batched entry points (device arrays, reference layouts) --------------------------------------------------------
 inline void compute_aabb_sphere_batch(mb200_stream st, int64_t n, const double* center, const double* radius, double* aabb) {
   check(mb200_compute_aabb_sphere(st, n, center, radius, aabb), "mb200_compute_aabb_sphere");
@@ -214,6 +251,121 @@ inline double distance(const LineSegment& seg, const Sphere& sph, Point& cp, dou
         "mb200_distance_segment_sphere");
   cp = detail::down3(cpd), sep = detail::down3(sv), t = dt.to_host()[0];
   return d.to_host()[0];
+}
+
+// ---- the remaining primitives ------------------------------------------------------------------
+namespace detail {
+inline DeviceVector<double> upq(const Quaternion& o) { return up({o.q[0], o.q[1], o.q[2], o.q[3]}); }
+}  // namespace detail
+inline AABB compute_aabb(const Point& p) {  // compute_aabb.hpp:47-54
+  auto a = detail::up3(p);
+  DeviceVector<double> out(6);
+  check(mb200_compute_aabb_point(nullptr, 1, a.data(), out.data()), "mb200_compute_aabb_point");
+  return detail::down_aabb(out);
+}
+inline AABB compute_aabb(const LineSegment& s) {  // compute_aabb.hpp:57-69
+  auto a = detail::up3(s.start()), b = detail::up3(s.end());
+  DeviceVector<double> out(6);
+  check(mb200_compute_aabb_line_segment(nullptr, 1, a.data(), b.data(), out.data()), "mb200_compute_aabb_line_segment");
+  return detail::down_aabb(out);
+}
+inline AABB compute_aabb(const Ellipsoid& e) {  // compute_aabb.hpp:83-103
+  auto c = detail::up3(e.center()), q = detail::upq(e.orientation()), r = detail::up3(e.radii());
+  DeviceVector<double> out(6);
+  check(mb200_compute_aabb_ellipsoid(nullptr, 1, c.data(), q.data(), r.data(), out.data()), "mb200_compute_aabb_ellipsoid");
+  return detail::down_aabb(out);
+}
+inline double distance(const Point& x, const Sphere& s, Vector3& sep) {  // distance/PointSphere.hpp:68-76
+  auto px = detail::up3(x), c = detail::up3(s.center()), r = detail::up({s.radius()});
+  DeviceVector<double> d(1), sv(3);
+  check(mb200_distance_point_sphere(nullptr, 1, px.data(), c.data(), r.data(), d.data(), sv.data()),
+        "mb200_distance_point_sphere");
+  sep = detail::down3(sv);
+  return d.to_host()[0];
+}
+/// distance/PointLine.hpp:92-103. As in the reference, sep is not written.
+inline double distance(const Point& x, const Line& line, Point& closest_point, double& arch_length, Vector3& /*sep*/) {
+  auto px = detail::up3(x), c = detail::up3(line.center()), dir = detail::up3(line.direction());
+  DeviceVector<double> d(1), cp(3), a(1);
+  check(mb200_distance_point_line(nullptr, 1, px.data(), c.data(), dir.data(), d.data(), cp.data(), a.data()),
+        "mb200_distance_point_line");
+  closest_point = detail::down3(cp), arch_length = a.to_host()[0];
+  return d.to_host()[0];
+}
+/// distance/LineLine.hpp:131-157. Parallel lines: returns 0 with sep = 0; closest points and arch lengths are then 0
+/// here (the reference leaves them untouched).
+inline double distance(const Line& l1, const Line& l2, Point& cp1, Point& cp2, double& arch1, double& arch2, Vector3& sep) {
+  auto c1 = detail::up3(l1.center()), d1 = detail::up3(l1.direction()), c2 = detail::up3(l2.center()),
+       d2 = detail::up3(l2.direction());
+  DeviceVector<double> d(1), p1(3), p2(3), a1(1), a2(1), sv(3);
+  check(mb200_distance_line_line(nullptr, 1, c1.data(), d1.data(), c2.data(), d2.data(), d.data(), p1.data(), p2.data(),
+                                 a1.data(), a2.data(), sv.data()),
+        "mb200_distance_line_line");
+  cp1 = detail::down3(p1), cp2 = detail::down3(p2), sep = detail::down3(sv);
+  arch1 = a1.to_host()[0], arch2 = a2.to_host()[0];
+  return d.to_host()[0];
+}
+/// distance/LineSphere.hpp:93-102 (sep inherits PointLine's behaviour: not written).
+inline double distance(const Line& line, const Sphere& s, Point& closest_point, double& arch_length, Vector3& /*sep*/) {
+  auto lc = detail::up3(line.center()), dir = detail::up3(line.direction()), c = detail::up3(s.center()),
+       r = detail::up({s.radius()});
+  DeviceVector<double> d(1), cp(3), a(1);
+  check(mb200_distance_line_sphere(nullptr, 1, lc.data(), dir.data(), c.data(), r.data(), d.data(), cp.data(), a.data()),
+        "mb200_distance_line_sphere");
+  closest_point = detail::down3(cp), arch_length = a.to_host()[0];
+  return d.to_host()[0];
+}
+/// distance/PointEllipsoid.hpp:97-135
+inline double distance(SharedNormalSigned, const Point& x, const Ellipsoid& e, Point& closest_point, Vector3& ellipsoid_normal) {
+  auto px = detail::up3(x), c = detail::up3(e.center()), q = detail::upq(e.orientation()), r = detail::up3(e.radii());
+  DeviceVector<double> d(1), cp(3), nn(3);
+  check(mb200_distance_point_ellipsoid(nullptr, 1, px.data(), c.data(), q.data(), r.data(), d.data(), cp.data(), nn.data()),
+        "mb200_distance_point_ellipsoid");
+  closest_point = detail::down3(cp), ellipsoid_normal = detail::down3(nn);
+  return d.to_host()[0];
+}
+inline double distance(SharedNormalSigned t, const Point& x, const Ellipsoid& e) {
+  Point cp;
+  Vector3 n;
+  return distance(t, x, e, cp, n);
+}
+inline double distance(const Point& x, const Ellipsoid& e) { return distance(SharedNormalSigned{}, x, e); }
+/// distance/EllipsoidEllipsoid.hpp:109-151
+inline double distance(SharedNormalSigned, const Ellipsoid& e1, const Ellipsoid& e2, Point& cp1, Point& cp2,
+                       Vector3& shared_normal1, Vector3& shared_normal2) {
+  auto c1 = detail::up3(e1.center()), q1 = detail::upq(e1.orientation()), r1 = detail::up3(e1.radii());
+  auto c2 = detail::up3(e2.center()), q2 = detail::upq(e2.orientation()), r2 = detail::up3(e2.radii());
+  DeviceVector<double> d(1), p1(3), p2(3), nn(3);
+  check(mb200_distance_ellipsoid_ellipsoid(nullptr, 1, c1.data(), q1.data(), r1.data(), c2.data(), q2.data(), r2.data(),
+                                           d.data(), p1.data(), p2.data(), nn.data()),
+        "mb200_distance_ellipsoid_ellipsoid");
+  cp1 = detail::down3(p1), cp2 = detail::down3(p2), shared_normal1 = detail::down3(nn);
+  shared_normal2 = Vector3(-shared_normal1[0], -shared_normal1[1], -shared_normal1[2]);
+  return d.to_host()[0];
+}
+inline double distance(SharedNormalSigned t, const Ellipsoid& e1, const Ellipsoid& e2) {
+  Point a, b;
+  Vector3 n1, n2;
+  return distance(t, e1, e2, a, b, n1, n2);
+}
+inline double distance(const Ellipsoid& e1, const Ellipsoid& e2) { return distance(SharedNormalSigned{}, e1, e2); }
+/// distance/Circle3DCircle3D.hpp:88-151
+inline double distance(Euclidean, const Circle3D& k1, const Circle3D& k2, Point& cp1, Point& cp2, Vector3& shared_normal1,
+                       Vector3& shared_normal2) {
+  auto c1 = detail::up3(k1.center()), q1 = detail::upq(k1.orientation()), r1 = detail::up({k1.radius()});
+  auto c2 = detail::up3(k2.center()), q2 = detail::upq(k2.orientation()), r2 = detail::up({k2.radius()});
+  DeviceVector<double> d(1), p1(3), p2(3), nn(3);
+  check(mb200_distance_circle3d_circle3d(nullptr, 1, c1.data(), q1.data(), r1.data(), c2.data(), q2.data(), r2.data(),
+                                         d.data(), p1.data(), p2.data(), nn.data()),
+        "mb200_distance_circle3d_circle3d");
+  cp1 = detail::down3(p1), cp2 = detail::down3(p2), shared_normal1 = detail::down3(nn);
+  shared_normal2 = Vector3(-shared_normal1[0], -shared_normal1[1], -shared_normal1[2]);
+  return d.to_host()[0];
+}
+inline double distance(const Circle3D& k1, const Circle3D& k2) {
+  Point a, b;
+  Vector3 n1, n2;
+  return distance(Euclidean{}, k1, k2, a, b, n1, n2);
 }
 
 // ---- periodic metrics (periodicity.hpp) ------------------------------------------------------------------------------

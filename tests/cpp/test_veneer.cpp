@@ -62,8 +62,48 @@ int main() {
   expect_aabb(geom::compute_aabb(Spherocylinder{Point{1, -2, 3}, x90, 2, 3}), -1, -5.5, 1, 3, 1.5, 5);
   expect_aabb(geom::compute_aabb(SpherocylinderSegment{Point{1, -2, 3}, Point{1, -2, 3}, 4}), -3, -6, -1, 5, 2, 7);
   expect_aabb(geom::compute_aabb(SpherocylinderSegment{Point{1, -3.5, 3}, Point{1, -0.5, 3}, 2}), -1, -5.5, 1, 3, 1.5, 5);
+  // remaining primitives (UnitTestComputeAABB.cpp:137-205)
+  expect_aabb(geom::compute_aabb(Point{1, -2, 3}), 1, -2, 3, 1, -2, 3);
+  expect_aabb(geom::compute_aabb(LineSegment{Point{4, 5, 6}, Point{1, -2, 3}}), 1, -2, 3, 4, 5, 6);
+  expect_aabb(geom::compute_aabb(geom::Ellipsoid{Point{1, -2, 3}, Quaternion{1, 0, 0, 0}, geom::Vector3{4, 5, 6}}), -3, -7,
+              -3, 5, 3, 9);
+  expect_aabb(geom::compute_aabb(geom::Ellipsoid{Point{1, -2, 3}, x90, geom::Vector3{4, 5, 6}}), -3, -8, -2, 5, 4, 8);
   EXPECT_TRUE(geom::intersects(AABB({0, 0, 0}, {1, 1, 1}), AABB({1, 1, 1}, {2, 2, 2})));   // touching counts
   EXPECT_TRUE(!geom::intersects(AABB({0, 0, 0}, {1, 1, 1}), AABB({1.1, 0, 0}, {2, 1, 1})));
+
+  // ---- distance, remaining primitives ----
+  {
+    // UnitTestEllipsoidEllipsoid.cpp:119-235, tolerance 1e-4 (:53)
+    const Quaternion id{1, 0, 0, 0}, x_to_y{c45, 0, 0, c45};
+    const geom::Ellipsoid e0{Point{0, 0, 0}, id, 3.0, 1.0, 2.0};
+    EXPECT_NEAR(geom::distance(geom::SharedNormalSigned{}, e0, e0), -2.0, 1e-4);
+    EXPECT_NEAR(geom::distance(e0, geom::Ellipsoid{Point{0, 0, 0}, id, 6.0, 2.0, 4.0}), -3.0, 1e-4);
+    for (double want : {0.2, -0.2, 0.0}) {
+      const geom::Ellipsoid a{Point{-3.0 - 0.5 * want, 0, 0}, id, 3.0, 1.0, 2.0}, b{Point{3.0 + 0.5 * want, 0, 0}, id, 3.0, 1.0, 2.0};
+      Point p1, p2;
+      geom::Vector3 n1, n2;
+      EXPECT_NEAR(geom::distance(geom::SharedNormalSigned{}, a, b, p1, p2, n1, n2), want, 1e-4);
+      EXPECT_NEAR(n1[0], 1.0, 1e-4);
+      EXPECT_NEAR(n2[0], -1.0, 1e-4);
+      const geom::Ellipsoid up{Point{0, 4.0 + want, 0}, x_to_y, 3.0, 1.0, 2.0};
+      EXPECT_NEAR(geom::distance(up, e0), want, 1e-4);
+    }
+    // a sphere written as an ellipsoid (:54-117)
+    EXPECT_NEAR(geom::distance(Point{4, 4, 2}, geom::Ellipsoid{Point{0, 0, 0}, x90, 2.5, 2.5, 2.5}), 3.5, 1e-4);
+    geom::Vector3 sep;
+    EXPECT_NEAR(geom::distance(Point{4, 4, 2}, Sphere{Point{0, 0, 0}, 2.5}, sep), 3.5, 1e-14);
+    // skew lines x-axis and (0,1,z): distance 1 at arch lengths 0 / 0
+    Point q1, q2;
+    double a1, a2;
+    EXPECT_NEAR(geom::distance(geom::Line{Point{0, 0, 0}, {1, 0, 0}}, geom::Line{Point{0, 1, 0}, {0, 0, 1}}, q1, q2, a1, a2, sep),
+                1.0, 1e-14);
+    EXPECT_NEAR(sep[1], 1.0, 1e-14);
+    EXPECT_NEAR(geom::distance(Point{3, 4, 0}, geom::Line{Point{0, 0, 0}, {1, 0, 0}}, q1, a1, sep), 4.0, 1e-14);
+    EXPECT_NEAR(a1, 3.0, 1e-14);
+    EXPECT_NEAR(geom::distance(geom::Line{Point{0, 0, 0}, {1, 0, 0}}, Sphere{Point{3, 4, 0}, 1.5}, q1, a1, sep), 2.5, 1e-14);
+    // two unit circles in parallel planes one apart, coaxial: Euclidean distance 1
+    EXPECT_NEAR(geom::distance(geom::Circle3D{Point{0, 0, 0}, id, 1.0}, geom::Circle3D{Point{0, 0, 1}, id, 1.0}), 1.0, 1e-6);
+  }
 
   // ---- distance ----
   {
