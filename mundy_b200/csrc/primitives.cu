@@ -177,7 +177,7 @@ struct CircleCircle {  // in3 = {c1, c2}, in4 = {q1, q2}, in1 = {r1, r2}; out: d
 };
 
 template <class Op>
-int launch(mb200_stream stream, int64_t n, const PrimArgs& A, int ctas_per_sm = 4) {
+int launch(mb200_stream stream, int64_t n, const PrimArgs& A) {
   MB200_REQUIRE(n >= 0, "n < 0");
   if (n == 0) return MB200_OK;
   for (int k = 0; k < Op::N3; ++k) MB200_REQUIRE(A.in3[k], "null input");
@@ -185,7 +185,13 @@ int launch(mb200_stream stream, int64_t n, const PrimArgs& A, int ctas_per_sm = 
   for (int k = 0; k < Op::N1; ++k) MB200_REQUIRE(A.in1[k], "null input");
   if (Op::O6) MB200_REQUIRE(A.out6, "null output");
   MB200_TRY(require_device());
-  prim_kernel<Op><<<grid_for(n, kTile, kSMs * ctas_per_sm), kTile, 0, as_stream(stream)>>>(n, A);
+  // every tile is load -> barrier -> arithmetic -> barrier -> store, so the SM overlaps tiles only across CTAs: fill it
+  static const int per_sm = [] {
+    int b = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, prim_kernel<Op>, kTile, 0);
+    return b > 0 ? b : 1;
+  }();
+  prim_kernel<Op><<<grid_for(n, kTile, kSMs * per_sm), kTile, 0, as_stream(stream)>>>(n, A);
   MB200_LAUNCHED();
   return MB200_OK;
 }
@@ -235,21 +241,20 @@ int mb200_distance_line_sphere(mb200_stream stream, int64_t n, const double* lin
 int mb200_distance_point_ellipsoid(mb200_stream stream, int64_t n, const double* x, const double* center,
                                    const double* quat, const double* radii, double* dist, double* cp,
                                    double* normal) {
-  return launch<PointEllipsoid>(stream, n, PrimArgs{{x, center, radii}, {quat}, {}, {dist}, {cp, normal}, nullptr}, 8);
+  return launch<PointEllipsoid>(stream, n, PrimArgs{{x, center, radii}, {quat}, {}, {dist}, {cp, normal}, nullptr});
 }
 
 int mb200_distance_ellipsoid_ellipsoid(mb200_stream stream, int64_t n, const double* c1, const double* q1,
                                        const double* radii1, const double* c2, const double* q2,
                                        const double* radii2, double* dist, double* cp1, double* cp2, double* normal1) {
   return launch<EllipsoidEllipsoid>(stream, n,
-                                    PrimArgs{{c1, radii1, c2, radii2}, {q1, q2}, {}, {dist}, {cp1, cp2, normal1}, nullptr},
-                                    8);
+                                    PrimArgs{{c1, radii1, c2, radii2}, {q1, q2}, {}, {dist}, {cp1, cp2, normal1}, nullptr});
 }
 
 int mb200_distance_circle3d_circle3d(mb200_stream stream, int64_t n, const double* c1, const double* q1,
                                      const double* r1, const double* c2, const double* q2, const double* r2,
                                      double* dist, double* cp1, double* cp2, double* normal1) {
-  return launch<CircleCircle>(stream, n, PrimArgs{{c1, c2}, {q1, q2}, {r1, r2}, {dist}, {cp1, cp2, normal1}, nullptr}, 8);
+  return launch<CircleCircle>(stream, n, PrimArgs{{c1, c2}, {q1, q2}, {r1, r2}, {dist}, {cp1, cp2, normal1}, nullptr});
 }
 
 }  // extern "C"
