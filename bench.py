@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-stage-timers", action="store_true")
+    ap.add_argument("--stage-sample", type=int, default=8,
+                    help="bracket every k-th launch of the per-iteration LCP kernels with CUDA events (1 = every launch)")
     return ap.parse_args()
 
 
@@ -251,7 +253,7 @@ def run_b200(args):
 
     # ---- timed region: device-resident -----------------------------------------------------------------------------
     if not args.no_stage_timers:
-        ops.profile_enable(True)
+        ops.profile_enable(max(1, args.stage_sample))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = ops.kernel_launch_count()
     barrier()
@@ -270,6 +272,7 @@ def run_b200(args):
     launches = ops.kernel_launch_count() - launches0
     clocks = sampler.stop() if sampler else None
     stages = ops.profile_read() if not args.no_stage_timers else {}
+    stage_calls = ops.profile_calls() if not args.no_stage_timers else {}
     ops.profile_enable(False)
     tlog = list(log)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -359,7 +362,7 @@ def run_b200(args):
         nloc = mbd.local_counts(links)[0] if comm is not None else n  # bodies this rank works on (owned + ghosts)
         alg = {"lcp_rate": 128.0 * C + 64.0 * nloc, "lcp_body": 120.0 * C + 104.0 * nloc}
         for name, (tot_ms, cnt) in stages.items():
-            stage_out[name] = {"ms_total": round(tot_ms, 4), "regions": cnt}
+            stage_out[name] = {"ms_total": round(tot_ms, 4), "regions": cnt, "calls": stage_calls.get(name, cnt)}
             if name in alg and cnt > 0:
                 gbs = alg[name] / (tot_ms / cnt * 1e-3) / 1e9
                 stage_out[name].update({"alg_bytes": alg[name], "gbs": round(gbs, 1), "frac": round(gbs / peak, 4)})
@@ -375,15 +378,16 @@ def run_b200(args):
                 pass
             roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                        "launches": cnt, "avg_us": 1e3 * tot_ms / cnt,
-                        "share_of_step": tot_ms / ms}
-            it_ms = sum(stages[k][0] for k in ("lcp_rate", "lcp_body"))
-            its = stages["lcp_rate"][1]  # operator applications (one body pass + one contact pass each)
-            if its > 0:
+                        "launches": stage_calls.get(dom, cnt), "launches_timed": cnt, "avg_us": 1e3 * tot_ms / cnt,
+                        "share_of_step": (tot_ms / cnt) * stage_calls.get(dom, cnt) / ms,
+                        "timing": f"CUDA events around every {max(1, args.stage_sample)}-th launch inside the timed region"}
+            if stages["lcp_rate"][1] > 0 and stages["lcp_body"][1] > 0:
+                # one operator application = one body pass + one contact pass
+                it_ms = sum(stages[k][0] / stages[k][1] for k in ("lcp_rate", "lcp_body"))
                 it_bytes = 120.0 * C + 240.0 * nloc  # fused-ideal bytes of one rod BBPGD iteration
-                roofline["lcp_iteration"] = {"alg_bytes": it_bytes, "avg_us": 1e3 * it_ms / its,
-                                             "gbs": it_bytes / (it_ms / its * 1e-3) / 1e9,
-                                             "frac": it_bytes / (it_ms / its * 1e-3) / 1e9 / peak}
+                roofline["lcp_iteration"] = {"alg_bytes": it_bytes, "avg_us": 1e3 * it_ms,
+                                             "gbs": it_bytes / (it_ms * 1e-3) / 1e9,
+                                             "frac": it_bytes / (it_ms * 1e-3) / 1e9 / peak}
 
     cpu = None
     if not args.no_cpu_baseline:

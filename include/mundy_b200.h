@@ -486,7 +486,10 @@ int64_t mb200_kernel_launch_count(void);
  * 999-1053; here: CUDA events recorded on the stream the kernels are launched on). Off by default; while enabled every
  * launch of the listed stages is bracketed by an event pair. mb200_profile_read synchronises the recorded events,
  * returns the accumulated device time [ms] and the number of bracketed regions of one stage since the last
- * mb200_profile_enable(1), and keeps accumulating.
+ * mb200_profile_enable(1), and keeps accumulating. mb200_profile_enable(k), k > 1: of the per-launch stages (LCP_BODY,
+ * LCP_RATE, LCP_COMM) only every k-th region is bracketed (an event pair between back-to-back kernels costs about a
+ * launch gap: 4.5 % of a 1M-rod step when every launch is bracketed); mb200_profile_calls returns the number of regions
+ * entered, bracketed or not.
  * ------------------------------------------------------------------------------------------------------------- */
 enum mb200_stage {
   MB200_STAGE_TRIGGER = 0,    /* rebuild trigger (moved more than buffer/2)        one region per step   */
@@ -503,6 +506,7 @@ enum mb200_stage {
 };
 int mb200_profile_enable(int on);
 int mb200_profile_read(int stage, double* ms_total_h, int64_t* regions_h);
+int mb200_profile_calls(int stage, int64_t* calls_h);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -77,6 +77,7 @@ SIGNATURES = {
     "mb200_kernel_launch_count": (c_i64, []),
     "mb200_profile_enable": (C.c_int, [C.c_int]),
     "mb200_profile_read": (C.c_int, [C.c_int, P(c_dbl), P(c_i64)]),
+    "mb200_profile_calls": (C.c_int, [C.c_int, P(c_i64)]),
     "mb200_device_alloc": (C.c_int, [P(vp), c_i64]),
     "mb200_device_free": (C.c_int, [vp]),
     "mb200_copy_to_device": (C.c_int, [vp, vp, vp, c_i64]),

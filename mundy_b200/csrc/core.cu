@@ -19,6 +19,7 @@ std::vector<ProfRegion> g_prof_open;       // recorded, not yet folded into the 
 std::vector<cudaEvent_t> g_prof_free;      // recycled events
 double g_prof_ms[MB200_STAGE_COUNT];
 long long g_prof_regions[MB200_STAGE_COUNT];
+long long g_prof_calls[MB200_STAGE_COUNT];  // regions entered, bracketed or not
 
 cudaEvent_t prof_event() {
   if (!g_prof_free.empty()) {
@@ -47,6 +48,12 @@ void prof_fold() {  // g_prof_mu held
 
 int prof_begin(int stage, cudaStream_t st) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
+  // mb200_profile_enable(k > 1): of the per-launch stages (two or three regions per BBPGD iteration) only every k-th
+  // region is bracketed: an event pair between back-to-back kernels costs about as much as the launch gap it replaces
+  const int stride = g_profile_on.load(std::memory_order_relaxed);
+  const long long call = g_prof_calls[stage]++;
+  const bool per_launch = stage == MB200_STAGE_LCP_BODY || stage == MB200_STAGE_LCP_RATE || stage == MB200_STAGE_LCP_COMM;
+  if (per_launch && stride > 1 && call % stride != 0) return -1;
   ProfRegion r{stage, prof_event(), prof_event(), false};
   if (!r.a || !r.b) return -1;
   cudaEventRecord(r.a, st);
@@ -139,9 +146,10 @@ int mb200_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(mb200::g_prof_mu);
   mb200::prof_fold();
   if (on) {
-    for (int k = 0; k < MB200_STAGE_COUNT; ++k) mb200::g_prof_ms[k] = 0.0, mb200::g_prof_regions[k] = 0;
+    for (int k = 0; k < MB200_STAGE_COUNT; ++k)
+      mb200::g_prof_ms[k] = 0.0, mb200::g_prof_regions[k] = 0, mb200::g_prof_calls[k] = 0;
   }
-  mb200::g_profile_on.store(on ? 1 : 0);
+  mb200::g_profile_on.store(on > 0 ? on : 0);
   return MB200_OK;
 }
 
@@ -151,6 +159,13 @@ int mb200_profile_read(int stage, double* ms_total_h, int64_t* regions_h) {
   mb200::prof_fold();
   *ms_total_h = mb200::g_prof_ms[stage];
   *regions_h = mb200::g_prof_regions[stage];
+  return MB200_OK;
+}
+
+int mb200_profile_calls(int stage, int64_t* calls_h) {
+  MB200_REQUIRE(stage >= 0 && stage < MB200_STAGE_COUNT && calls_h, "bad stage or null output");
+  std::lock_guard<std::mutex> lk(mb200::g_prof_mu);
+  *calls_h = mb200::g_prof_calls[stage];
   return MB200_OK;
 }
 

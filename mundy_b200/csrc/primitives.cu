@@ -27,7 +27,7 @@ struct PrimArgs {
 // Op: static constexpr int N3, N4, N1 (inputs), O1, O3 (outputs), bool O6;
 //     static __device__ void run(const V3* a, const Q4* q, const double* s, double* o1, V3* o3, double* o6)
 template <class Op>
-__global__ void __launch_bounds__(kTile) prim_kernel(int64_t n, PrimArgs A) {
+__device__ __forceinline__ void prim_body(int64_t n, const PrimArgs& A) {
   constexpr int kIn = Op::N3 > 0 ? Op::N3 : 1;
   constexpr int kOut = Op::O6 ? 2 : (Op::O3 > 0 ? Op::O3 : 1);
   __shared__ __align__(16) double s_in[kIn][3 * kTile];
@@ -76,9 +76,21 @@ __global__ void __launch_bounds__(kTile) prim_kernel(int64_t n, PrimArgs A) {
   }
 }
 
+// Two entry points over the same body: the closed-form kernels take ptxas' own register count (29-62: five to eight
+// CTAs per SM; asking for a minimum made them slower), the Ellipsoid-Ellipsoid minimiser is compiled for two CTAs per SM
+// (128 registers instead of 254: 16 warps per SM hide its fp64 latency chains better, +13 % pairs/s).
+template <class Op>
+__global__ void __launch_bounds__(kTile) prim_kernel(int64_t n, PrimArgs A) {
+  prim_body<Op>(n, A);
+}
+template <class Op>
+__global__ void __launch_bounds__(kTile, 2) prim_kernel_2cta(int64_t n, PrimArgs A) {
+  prim_body<Op>(n, A);
+}
+
 #define MB200_PRIM_SHAPE(n3, n4, n1, o1, o3, o6) \
   static constexpr int N3 = n3, N4 = n4, N1 = n1, O1 = o1, O3 = o3; \
-  static constexpr bool O6 = o6
+  static constexpr bool O6 = o6, TWO_CTAS = false
 
 struct AabbPoint {  // compute_aabb.hpp:47-54
   MB200_PRIM_SHAPE(1, 0, 0, 0, 0, true);
@@ -162,7 +174,8 @@ struct PointEllipsoid {  // in3 = {point, centre, radii}, in4 = {orientation}; o
   }
 };
 struct EllipsoidEllipsoid {  // in3 = {c1, radii1, c2, radii2}, in4 = {q1, q2}; out: dist, cp1, cp2, normal of the first
-  MB200_PRIM_SHAPE(4, 2, 0, 1, 3, false);
+  static constexpr int N3 = 4, N4 = 2, N1 = 0, O1 = 1, O3 = 3;
+  static constexpr bool O6 = false, TWO_CTAS = true;
   static __device__ void run(const V3* a, const Q4* q, const double*, double* o1, V3* o3, double*) {
     const prim::Ellipsoid e1{a[0], q[0], a[1]}, e2{a[2], q[1], a[3]};
     o1[0] = prim::dist_ellipsoid_ellipsoid(e1, e2, o3[0], o3[1], o3[2]);
@@ -188,10 +201,16 @@ int launch(mb200_stream stream, int64_t n, const PrimArgs& A) {
   // every tile is load -> barrier -> arithmetic -> barrier -> store, so the SM overlaps tiles only across CTAs: fill it
   static const int per_sm = [] {
     int b = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, prim_kernel<Op>, kTile, 0);
+    if constexpr (Op::TWO_CTAS)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, prim_kernel_2cta<Op>, kTile, 0);
+    else
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, prim_kernel<Op>, kTile, 0);
     return b > 0 ? b : 1;
   }();
-  prim_kernel<Op><<<grid_for(n, kTile, kSMs * per_sm), kTile, 0, as_stream(stream)>>>(n, A);
+  if constexpr (Op::TWO_CTAS)
+    prim_kernel_2cta<Op><<<grid_for(n, kTile, kSMs * per_sm), kTile, 0, as_stream(stream)>>>(n, A);
+  else
+    prim_kernel<Op><<<grid_for(n, kTile, kSMs * per_sm), kTile, 0, as_stream(stream)>>>(n, A);
   MB200_LAUNCHED();
   return MB200_OK;
 }

@@ -440,7 +440,18 @@ STAGES = ("trigger", "broadphase", "pack", "narrow", "lcp_setup", "lcp_body", "l
 
 
 def profile_enable(on=True):
-    check(lib.mb200_profile_enable(int(bool(on))), "profile_enable")
+    """on = True / 1: every region is bracketed; on = k > 1: every k-th region of the per-launch LCP stages."""
+    check(lib.mb200_profile_enable(int(on)), "profile_enable")
+
+
+def profile_calls():
+    """{stage: regions entered since profile_enable, bracketed or not}."""
+    out = {}
+    for k, name in enumerate(STAGES):
+        cnt = C.c_int64(0)
+        check(lib.mb200_profile_calls(k, C.byref(cnt)), "profile_calls")
+        out[name] = cnt.value
+    return out
 
 
 def profile_read():
