@@ -75,6 +75,18 @@ class ClockSampler:
         except OSError:
             pass
 
+    def wait_ready(self, timeout=8.0):
+        """Blocks until nvidia-smi has written its first sample: its NVML start-up (process start + driver attach,
+        200-400 ms, during which CUDA calls of this process can stall for tens of ms) is then over. Observed without
+        this wait: a +24..58 ms hiccup in the 4th timed step of some runs."""
+        if self.p is None:
+            return
+        t0 = time.perf_counter()
+        while time.perf_counter() - t0 < timeout and self.p.poll() is None:
+            if os.path.getsize(self.f.name) > 0:
+                return
+            time.sleep(0.02)
+
     def mark(self):
         import datetime
         self.t0 = datetime.datetime.now()
@@ -167,7 +179,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "lcp_iters_per_step": info["iters_per_step"], "links": info["links"],
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(args, n):
@@ -247,6 +259,9 @@ def run_b200(args):
     for _ in range(args.prep):
         step()
     sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.wait_ready()
+    barrier()
     for _ in range(args.warmup):
         step()
     log.clear()
@@ -410,13 +425,31 @@ def run_b200(args):
         line["dist"] = {"rank0_local_bodies": nl, "rank0_ghost_rows": ng, "owned_per_rank": n,
                         "exchange": comm.exchange_mode,
                         "note": "links_per_step, stages and roofline are rank 0's"}
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else that writes to fd 1 (NCCL prints its
+    version banner there from C) was redirected to stderr in main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    global _JSON_FD
     args = parse_args()
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -26,6 +26,16 @@ struct mb200_neighbor_links {
   // device mirrors of the host arrays of mb200_collision_step_host
   mb200::DevBuf<double> hm_center, hm_quat, hm_radius, hm_length, hm_fext, hm_text, hm_fcol, hm_tcol, hm_u, hm_w;
   mb200::DevBuf<int32_t> hm_kind;
+  // mb200_collision_step_host: the external wrench is uploaded on a side stream behind the body arrays, while the
+  // rebuild trigger and the link rebuild (which do not read it) run; the step waits for forces_ev before its first use
+  cudaStream_t copy_st = nullptr;
+  cudaEvent_t bodies_ev = nullptr, forces_ev = nullptr;
+  bool forces_pending = false;
+  ~mb200_neighbor_links() {
+    if (bodies_ev) cudaEventDestroy(bodies_ev);
+    if (forces_ev) cudaEventDestroy(forces_ev);
+    if (copy_st) cudaStreamDestroy(copy_st);
+  }
 
   // ---- multi-GPU state (dist_step.cu) ----
   struct Dist {

@@ -213,6 +213,10 @@ int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodi
       }
     }
     MB200_TRY(h->rec.reserve(static_cast<size_t>(rods ? 3 : 1) * C + 1));
+    if (h->forces_pending) {  // host entry point: the wrench arrives on the side stream (first read just below)
+      MB200_CUDA(cudaStreamWaitEvent(st, h->forces_ev, 0));
+      h->forces_pending = false;
+    }
     {
       StageScope ps(MB200_STAGE_PACK, st);
       MB200_TRY(pack_bodies(st, bodies, reinterpret_cast<const int32_t*>(h->perm.p), h->b0.p, rods ? h->b1.p : nullptr));
@@ -303,8 +307,26 @@ extern "C" int mb200_collision_step_host(mb200_neighbor_links* h, mb200_stream s
     MB200_TRY(h->hm_kind.reserve(n + 4));
     MB200_CUDA(cudaMemcpyAsync(h->hm_kind.p, bh->kind, n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   }
-  if (F_ext_h) MB200_TRY(up(h->hm_fext, F_ext_h, 3 * n));
-  if (T_ext_h && rods) MB200_TRY(up(h->hm_text, T_ext_h, 3 * n));
+  if (n > 0 && (F_ext_h || (T_ext_h && rods))) {
+    if (!h->copy_st) {
+      MB200_CUDA(cudaStreamCreateWithFlags(&h->copy_st, cudaStreamNonBlocking));
+      MB200_CUDA(cudaEventCreateWithFlags(&h->bodies_ev, cudaEventDisableTiming));
+      MB200_CUDA(cudaEventCreateWithFlags(&h->forces_ev, cudaEventDisableTiming));
+    }
+    // behind the body arrays on the link (the search needs those first), concurrent with the trigger and the rebuild
+    MB200_CUDA(cudaEventRecord(h->bodies_ev, st));
+    MB200_CUDA(cudaStreamWaitEvent(h->copy_st, h->bodies_ev, 0));
+    if (F_ext_h) {
+      MB200_TRY(h->hm_fext.reserve(3 * n + 4));
+      MB200_CUDA(cudaMemcpyAsync(h->hm_fext.p, F_ext_h, 3 * n * d, cudaMemcpyHostToDevice, h->copy_st));
+    }
+    if (T_ext_h && rods) {
+      MB200_TRY(h->hm_text.reserve(3 * n + 4));
+      MB200_CUDA(cudaMemcpyAsync(h->hm_text.p, T_ext_h, 3 * n * d, cudaMemcpyHostToDevice, h->copy_st));
+    }
+    MB200_CUDA(cudaEventRecord(h->forces_ev, h->copy_st));
+    h->forces_pending = true;
+  }
   if (F_col_h) MB200_TRY(h->hm_fcol.reserve(3 * n + 4));
   if (T_col_h && rods) MB200_TRY(h->hm_tcol.reserve(3 * n + 4));
   if (U_out_h) MB200_TRY(h->hm_u.reserve(3 * n + 4));
@@ -315,6 +337,10 @@ extern "C" int mb200_collision_step_host(mb200_neighbor_links* h, mb200_stream s
                                           (T_ext_h && rods) ? h->hm_text.p : nullptr, F_col_h ? h->hm_fcol.p : nullptr,
                                           (T_col_h && rods) ? h->hm_tcol.p : nullptr, U_out_h ? h->hm_u.p : nullptr,
                                           (W_out_h && rods) ? h->hm_w.p : nullptr, stats_h);
+  if (h->forces_pending) {  // the step returned before it consumed the wrench (n == 0 or an error): drain the side stream
+    cudaStreamSynchronize(h->copy_st);
+    h->forces_pending = false;
+  }
   if (status != MB200_OK) return status;
   MB200_CUDA(cudaMemcpyAsync(bh->center, h->hm_center.p, 3 * n * d, cudaMemcpyDeviceToHost, st));
   if (rods) MB200_CUDA(cudaMemcpyAsync(bh->quat, h->hm_quat.p, 4 * n * d, cudaMemcpyDeviceToHost, st));
