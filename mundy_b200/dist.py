@@ -48,6 +48,62 @@ def hilbert_index(cells, bits):
     return h
 
 
+# The eight sub-cubes of the reference's recursive generator (mundy/math/src/mundy_math/Hilbert.hpp:48-85), in visiting
+# order: (coefficients of (dr1, dr2, dr3) locating the sub-cube, its frame as signed picks (sign, index) of the parent's
+# directors). E.g. the first recursive call is hilbert_3d(snew, i, ..., current_position_new, dr2, dr3, dr1).
+_HILBERT_CHILDREN = (
+    ((0, 0, 0), ((+1, 1), (+1, 2), (+1, 0))),
+    ((1, 0, 0), ((+1, 2), (+1, 0), (+1, 1))),
+    ((1, 1, 0), ((+1, 2), (+1, 0), (+1, 1))),
+    ((0, 1, 0), ((-1, 0), (-1, 1), (+1, 2))),
+    ((0, 1, 1), ((-1, 0), (-1, 1), (+1, 2))),
+    ((1, 1, 1), ((-1, 2), (+1, 0), (-1, 1))),
+    ((1, 0, 1), ((-1, 2), (+1, 0), (-1, 1))),
+    ((0, 0, 1), ((+1, 1), (-1, 2), (-1, 0))),
+)
+
+
+def hilbert_index_reference(cells, bits):
+    """Position of every lattice cell (n, 3) in [0, 2^bits)^3 along the REFERENCE's Hilbert curve: the visiting order of
+    math::hilbert_3d(s = 2^bits, start (0,0,0), frame (x, y, z)) (Hilbert.hpp:48-85; goldens UnitTestHilbert.cpp:48-295),
+    found by descending that recursion for all cells at once instead of enumerating the 8^bits lattice points.
+    Invariant of the recursion used here: `current_position` is always the minimum corner of the sub-cube; the curve
+    enters at that corner shifted by snew along every axis a director points down (Hilbert.hpp:63-66)."""
+    p = np.asarray(cells, dtype=np.int64)
+    n = len(p)
+    corner = np.zeros((n, 3), dtype=np.int64)
+    D = np.tile(np.eye(3, dtype=np.int64)[None], (n, 1, 1))  # D[:, k, :] = dr_{k+1}
+    idx = np.zeros(n, dtype=np.uint64)
+    s = 1 << bits
+    while s > 1:
+        sn = s // 2
+        start = corner - sn * np.minimum(D, 0).sum(axis=1)
+        which = np.full(n, -1, dtype=np.int64)
+        new_corner, new_D = np.zeros_like(corner), np.zeros_like(D)
+        for k, (combo, frame) in enumerate(_HILBERT_CHILDREN):
+            ck = start + sn * (combo[0] * D[:, 0, :] + combo[1] * D[:, 1, :] + combo[2] * D[:, 2, :])
+            sel = np.all((p >= ck) & (p < ck + sn), axis=1) & (which < 0)
+            which[sel] = k
+            new_corner[sel] = ck[sel]
+            new_D[sel] = np.stack([sg * D[sel, j, :] for sg, j in frame], axis=1)
+        assert (which >= 0).all(), "cell outside the lattice"
+        idx = idx * np.uint64(8) + which.astype(np.uint64)
+        corner, D, s = new_corner, new_D, sn
+    return idx
+
+
+def morton_key(cells):
+    """The device's cell key (csrc/broadphase.cu:42-44 morton3): bit b of x, y, z -> bits 3b, 3b + 1, 3b + 2, i.e. z is the
+    most significant axis. Sorting by it is the order of zorder_knn::Less<Point, 3> (mundy/math/src/mundy_math/zmort.hpp:
+    195-220) on non-negative integer coordinates (tests/test_sfc_cpu.py). 10 bits per axis."""
+    c = np.asarray(cells, dtype=np.uint64)
+    key = np.zeros(len(c), dtype=np.uint64)
+    for b in range(10):
+        for d in range(3):
+            key |= ((c[:, d] >> np.uint64(b)) & np.uint64(1)) << np.uint64(3 * b + d)
+    return key
+
+
 def hilbert_order(center, bits=10):
     """Permutation that sorts the bodies along the Hilbert curve of their centres (2^bits cells per axis)."""
     center = np.asarray(center, dtype=np.float64)
@@ -55,9 +111,8 @@ def hilbert_order(center, bits=10):
     span = float(np.max(hi - lo))
     span = span if span > 0 else 1.0
     cells = np.minimum(((center - lo) / span * (1 << bits)).astype(np.int64), (1 << bits) - 1)
-    # axes passed as (z, y, x): the curve then starts along x like the reference's generator
-    # (mundy/math/tests/unit_tests/UnitTestHilbert.cpp:47-66, the 2^3 golden order)
-    return np.argsort(hilbert_index(cells[:, ::-1], bits), kind="stable")
+    # the reference's own curve (Hilbert.hpp:48-85): visiting order pinned against hilbert_3d for 2^3 .. 16^3 lattices
+    return np.argsort(hilbert_index_reference(cells, bits), kind="stable")
 
 
 def reorder(workload, order):

@@ -100,6 +100,24 @@ def rotate_quaternion(quat, omega, dt, lib=None, prefix="orc_"):
     return q
 
 
+# ---- space-filling-curve specifications, reference library only -----------------------------------
+def ref_hilbert_3d(s):
+    """Lattice points of the reference's hilbert_3d(s) in visiting order, (s^3, 3) ints (needs oracle/_ref)."""
+    out = np.zeros((s ** 3, 3))
+    _call(ref, "ref_hilbert_3d", int(s), out)
+    return out.astype(np.int64)
+
+
+def ref_zorder_less(p, q, which=0):
+    """which = 0: zorder_knn::Less<Point, 3>; 1: mundy::math::zmorton_less (zmort.hpp). Returns a bool array."""
+    p, q = _a(p), _a(q)
+    out = np.zeros(len(p), dtype=np.int32)
+    fn = ref.ref_zorder_less
+    fn.restype = None
+    fn(C.c_long(len(p)), C.c_int(which), _p(p), _p(q), _p(out))
+    return out.astype(bool)
+
+
 # ---- remaining primitives (SURVEY 8f rank 4): one generic front-end, outputs shaped by PRIMITIVE_OUTPUTS ------------
 # name -> per-item widths of the output arrays, in call order
 PRIMITIVE_OUTPUTS = {
