@@ -63,32 +63,59 @@ _HILBERT_CHILDREN = (
 )
 
 
+def _hilbert_tables():
+    """The recursion as an automaton: state = the frame (dr1, dr2, dr3), one of the signed axis permutations reachable from
+    (x, y, z); input = the octant of the cell inside the current cube (one bit per axis); output = which of the eight
+    recursive calls covers that octant, and the frame it is called with. Built by running the recursion's own arithmetic
+    on unit cubes (snew = 1)."""
+    eye = np.eye(3, dtype=np.int64)
+    states, index, todo = [], {}, [tuple(map(tuple, eye))]
+    rows_k, rows_next = [], []
+    while todo:
+        f = todo.pop()
+        if f in index:
+            continue
+        index[f] = len(states)
+        states.append(f)
+        D = np.array(f, dtype=np.int64)
+        start = -np.minimum(D, 0).sum(axis=0)  # entry corner relative to the minimum corner, in units of snew
+        ks, nxt = [None] * 8, [None] * 8
+        for k, (combo, frame) in enumerate(_HILBERT_CHILDREN):
+            off = start + combo[0] * D[0] + combo[1] * D[1] + combo[2] * D[2]  # child's minimum corner / snew
+            assert off.min() >= 0 and off.max() <= 1
+            octant = int(off[0]) | (int(off[1]) << 1) | (int(off[2]) << 2)
+            child = tuple(tuple(int(v) for v in sg * D[j]) for sg, j in frame)
+            assert ks[octant] is None
+            ks[octant], nxt[octant] = k, child
+            todo.append(child)
+        rows_k.append(ks)
+        rows_next.append(nxt)
+    T_k = np.array(rows_k, dtype=np.uint64)
+    T_next = np.array([[index[c] for c in row] for row in rows_next], dtype=np.int64)
+    return T_k, T_next
+
+
+_HILBERT_TABLES = None
+
+
 def hilbert_index_reference(cells, bits):
     """Position of every lattice cell (n, 3) in [0, 2^bits)^3 along the REFERENCE's Hilbert curve: the visiting order of
     math::hilbert_3d(s = 2^bits, start (0,0,0), frame (x, y, z)) (Hilbert.hpp:48-85; goldens UnitTestHilbert.cpp:48-295),
-    found by descending that recursion for all cells at once instead of enumerating the 8^bits lattice points.
-    Invariant of the recursion used here: `current_position` is always the minimum corner of the sub-cube; the curve
-    enters at that corner shifted by snew along every axis a director points down (Hilbert.hpp:63-66)."""
+    found by descending that recursion for all cells at once (one table look-up per level, see _hilbert_tables) instead
+    of enumerating the 8^bits lattice points. Invariant of the recursion used: `current_position` is always the minimum
+    corner of the sub-cube; the curve enters at that corner shifted by snew along every axis a director points down
+    (Hilbert.hpp:63-66)."""
+    global _HILBERT_TABLES
+    if _HILBERT_TABLES is None:
+        _HILBERT_TABLES = _hilbert_tables()
+    T_k, T_next = _HILBERT_TABLES
     p = np.asarray(cells, dtype=np.int64)
-    n = len(p)
-    corner = np.zeros((n, 3), dtype=np.int64)
-    D = np.tile(np.eye(3, dtype=np.int64)[None], (n, 1, 1))  # D[:, k, :] = dr_{k+1}
-    idx = np.zeros(n, dtype=np.uint64)
-    s = 1 << bits
-    while s > 1:
-        sn = s // 2
-        start = corner - sn * np.minimum(D, 0).sum(axis=1)
-        which = np.full(n, -1, dtype=np.int64)
-        new_corner, new_D = np.zeros_like(corner), np.zeros_like(D)
-        for k, (combo, frame) in enumerate(_HILBERT_CHILDREN):
-            ck = start + sn * (combo[0] * D[:, 0, :] + combo[1] * D[:, 1, :] + combo[2] * D[:, 2, :])
-            sel = np.all((p >= ck) & (p < ck + sn), axis=1) & (which < 0)
-            which[sel] = k
-            new_corner[sel] = ck[sel]
-            new_D[sel] = np.stack([sg * D[sel, j, :] for sg, j in frame], axis=1)
-        assert (which >= 0).all(), "cell outside the lattice"
-        idx = idx * np.uint64(8) + which.astype(np.uint64)
-        corner, D, s = new_corner, new_D, sn
+    state = np.zeros(len(p), dtype=np.int64)
+    idx = np.zeros(len(p), dtype=np.uint64)
+    for level in range(bits - 1, -1, -1):
+        octant = ((p[:, 0] >> level) & 1) | (((p[:, 1] >> level) & 1) << 1) | (((p[:, 2] >> level) & 1) << 2)
+        idx = (idx << np.uint64(3)) | T_k[state, octant]
+        state = T_next[state, octant]
     return idx
 
 
