@@ -155,13 +155,8 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
   const D4 si = ldg256(sr + i);
   // multi-GPU: links between two ghost bodies belong to other ranks
   const bool own_i = own ? own[i] != 0 : true;
-  D4 b0i{0, 0, 0, 0}, b1i{0, 0, 0, 0};
-  uint32_t pi = 0;
-  if (FILTER) {
-    b0i = ldg256(b0 + i);
-    b1i = ldg256(b1 + i);
-    pi = perm[i];
-  }
+  // (the shape filter's records of body i are re-read where they are used: one broadcast L1 hit per batch instead of 17
+  // registers held across the candidate loop)
   const int cx = cell_coord(si.x, gp, 0);
   const int cy = cell_coord(si.y, gp, 1);
   const int cz = cell_coord(si.z, gp, 2);
@@ -219,13 +214,16 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
   __syncwarp();
   const int* wpre = s_pre[wib];
   const int* wbeg = s_beg[wib];
-  auto candidate = [&](int t) {  // flattened index -> body index
-    int lo = 0, hi = nvalid - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (wpre[mid] <= t) lo = mid; else hi = mid - 1;
-    }
-    return wbeg[lo] + (t - wpre[lo]);
+  // flattened index tb0 + lane -> body index. Lane r keeps the prefix of the cell of rank r; the cells that start inside
+  // a batch of 32 consecutive indices are marked in one warp-wide OR, so a lane finds its cell with two population counts
+  // instead of a binary search through shared memory.
+  const int rpre = (lane < nvalid) ? wpre[lane] : 0x7fffffff;
+  auto candidate = [&](int tb0) {
+    const uint32_t below = __ballot_sync(0xffffffffu, rpre <= tb0);  // rank 0 starts at 0: never empty
+    const int rel = rpre - tb0;
+    const uint32_t starts = __reduce_or_sync(0xffffffffu, (rel > 0 && rel < 32) ? (1u << rel) : 0u);
+    const int lo = __popc(below) - 1 + __popc(starts & ((2u << lane) - 1u));
+    return wbeg[lo] + (tb0 + lane - wpre[lo]);
   };
 
   uint32_t total = 0;
@@ -247,6 +245,8 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
     bool keep = false;
     if (j >= 0) {
       // evaluate in the caller's (i<j) order so that the decision is bit-identical to the reference order
+      const D4 b0i = ldg256(b0 + i), b1i = ldg256(b1 + i);
+      const uint32_t pi = __ldg(perm + i);
       const D4 b0j = ldg256(b0 + j), b1j = ldg256(b1 + j);
       // operands are put in caller order first, so that the (long) distance code runs once per batch and not once per
       // order under divergence
@@ -267,8 +267,9 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
   };
   for (int t0 = 0; t0 < total_cand; t0 += 64) {
     const int ta = t0 + lane, tb = t0 + 32 + lane;
-    const int ja = (ta < total_cand) ? candidate(ta) : -1;
-    const int jb = (tb < total_cand) ? candidate(tb) : -1;
+    const int ca = candidate(t0), cb = candidate(t0 + 32);  // warp-wide: called by all lanes
+    const int ja = (ta < total_cand) ? ca : -1;
+    const int jb = (tb < total_cand) ? cb : -1;
     D4 sa{0, 0, 0, 0}, sb{0, 0, 0, 0};
     if (ja >= 0) sa = ldg256(sr + ja);
     if (jb >= 0) sb = ldg256(sr + jb);
