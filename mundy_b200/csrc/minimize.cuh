@@ -12,6 +12,11 @@
 #pragma once
 #include "common.cuh"
 
+// Every function is __host__ __device__: tests/cpp/host_minimize_check.cu instantiates this file's HOST side and
+// tests/test_primitives_cpu.py checks it bit for bit against the reference (no GPU needed). The library itself exports
+// device paths only.
+#define MB200_HD __host__ __device__
+
 namespace mb200 {
 namespace prim {
 
@@ -22,104 +27,102 @@ constexpr double kPi = 3.141592653589793238462643383279502884;
 struct V2 {
   double a, b;
 };
-__device__ inline V2 operator+(const V2& u, const V2& v) { return {u.a + v.a, u.b + v.b}; }
-__device__ inline V2 operator-(const V2& u, const V2& v) { return {u.a - v.a, u.b - v.b}; }
-__device__ inline V2 operator*(double s, const V2& v) { return {s * v.a, s * v.b}; }
-__device__ inline V2 neg(const V2& v) { return {-v.a, -v.b}; }
-__device__ inline double dot2(const V2& u, const V2& v) { return u.a * v.a + u.b * v.b; }
+MB200_HD inline V2 operator+(const V2& u, const V2& v) { return {u.a + v.a, u.b + v.b}; }
+MB200_HD inline V2 operator-(const V2& u, const V2& v) { return {u.a - v.a, u.b - v.b}; }
+MB200_HD inline V2 operator*(double s, const V2& v) { return {s * v.a, s * v.b}; }
+MB200_HD inline V2 neg(const V2& v) { return {-v.a, -v.b}; }
+MB200_HD inline double dot2(const V2& u, const V2& v) { return u.a * v.a + u.b * v.b; }
 
-__device__ inline Q4 qconj(const Q4& q) { return {q.w, -q.x, -q.y, -q.z}; }
+MB200_HD inline Q4 qconj(const Q4& q) { return {q.w, -q.x, -q.y, -q.z}; }
 
 // mundy/math/src/mundy_math/impl/minimize_impl.hpp:42-45
-__device__ inline double put_in_range(double lo, double hi, double v) { return (v < lo) ? lo : (v > hi) ? hi : v; }
+MB200_HD inline double put_in_range(double lo, double hi, double v) { return (v < lo) ? lo : (v > hi) ? hi : v; }
 
-// minimize_impl.hpp:52-80  (cubic through two values and two slopes)
-__device__ inline double poly_min_extrap(double f0, double d0, double f1, double d1, double limit = 1.0) {
+// Minimiser in [0, limit] of the cubic through two values and two slopes at 0 and 1 (minimize_impl.hpp:52-80).
+MB200_HD inline double cubic_minimiser(double f0, double d0, double f1, double d1, double limit = 1.0) {
   const double n = 3 * (f1 - f0) - 2 * d0 - d1;
   const double e = d0 + d1 - 2 * (f1 - f0);
-  const double temp_sqr = fmax(n * n - 3 * e * d0, 0.0);
-  if (temp_sqr < 0) return 0.5;
-  if (fabs(e) <= kEps) return 0.5;
-  const double temp = sqrt(temp_sqr);
-  const double x1 = (temp - n) / (3 * e);
-  const double x2 = -(temp + n) / (3 * e);
+  const double disc = fmax(n * n - 3 * e * d0, 0.0);
+  if (disc < 0 || fabs(e) <= kEps) return 0.5;
+  const double root = sqrt(disc);
+  const double x1 = (root - n) / (3 * e);
+  const double x2 = -(root + n) / (3 * e);
   const double y1 = f0 + d0 * x1 + n * x1 * x1 + e * x1 * x1 * x1;
   const double y2 = f0 + d0 * x2 + n * x2 * x2 + e * x2 * x2 * x2;
-  const double x = (y1 < y2) ? x1 : x2;
-  return put_in_range(0, limit, x);
+  return put_in_range(0, limit, (y1 < y2) ? x1 : x2);
 }
 
-// minimize_impl.hpp:233-398  line_search(f, f0, der, d0, rho, sigma, min_f, max_iter); F(alpha) returns the value, the
-// derivative is the central difference (F(alpha + eps) - F(alpha - eps)) / ((alpha + eps) - (alpha - eps)) (:217-220)
+// One evaluation of the search function: step length, value, central-difference slope.
+struct Probe {
+  double step, value, slope;
+};
+
+// Wolfe line search of minimize_impl.hpp:233-398 (strong Wolfe conditions with constants rho, sigma; a bracketing
+// phase that extrapolates by factors 1.4 .. 9, then a sectioning phase that keeps the trial inside [0.1, 0.5] of the
+// bracket), evaluation for evaluation in the reference's order. phi(step) is the objective along the search direction;
+// its slope is the central difference (phi(x + h) - phi(x - h)) / ((x + h) - (x - h)) (:217-220).
 template <class F>
-__device__ inline double line_search(const F& f, double f0, double d0, double rho, double sigma, double min_f, size_t max_iter,
-                          double eps) {
-  auto der = [&](double x) { return (f(x + eps) - f(x - eps)) / ((x + eps) - (x - eps)); };
-  const double tau1a = 1.4, tau1b = 9, tau2 = 1.0 / 10.0, tau3 = 1.0 / 2.0;
-  if (fabs(d0) <= fabs(f0) * kEps) return 0;
-  if (f0 <= min_f) return 0;
-  const double mu = (min_f - f0) / (rho * d0);
-  double alpha = 1;
-  if (mu < 0) alpha = -alpha;
-  alpha = put_in_range(0, 0.65 * mu, alpha);
-  double last_alpha = 0, last_val = f0, last_val_der = d0;
-  double a, b, a_val, b_val, a_val_der, b_val_der;
-  const double thresh = fabs(sigma * d0);
-  size_t itr = 0;
-  while (true) {
-    ++itr;
-    const double val = f(alpha);
-    const double val_der = der(alpha);
-    if (val <= min_f) return alpha;
-    if (val > f0 + rho * alpha * d0 || val >= last_val) {
-      a_val = last_val, a_val_der = last_val_der, b_val = val, b_val_der = val_der;
-      a = last_alpha, b = alpha;
+MB200_HD inline double line_search(const F& phi, double phi0, double slope0, double rho, double sigma,
+                                     double floor_value, int max_evals, double h) {
+  auto probe = [&](double x) {
+    Probe p;
+    p.step = x;
+    p.value = phi(x);
+    p.slope = (phi(x + h) - phi(x - h)) / ((x + h) - (x - h));
+    return p;
+  };
+  auto too_high = [&](const Probe& p) { return p.value > phi0 + rho * p.step * slope0; };  // no sufficient decrease
+  if (fabs(slope0) <= fabs(phi0) * kEps) return 0;
+  if (phi0 <= floor_value) return 0;
+  const double step_cap = (floor_value - phi0) / (rho * slope0);
+  const double flat = fabs(sigma * slope0);
+  double trial = put_in_range(0, 0.65 * step_cap, (step_cap < 0) ? -1.0 : 1.0);
+  Probe prev{0.0, phi0, slope0}, lo, hi;
+  int evals = 0;
+  for (;;) {  // bracketing: walk outwards until the minimum along the direction is enclosed
+    ++evals;
+    const Probe cur = probe(trial);
+    if (cur.value <= floor_value) return cur.step;
+    if (too_high(cur) || cur.value >= prev.value) {
+      lo = prev, hi = cur;
       break;
     }
-    if (fabs(val_der) <= thresh) return alpha;
-    if (last_alpha == alpha || itr >= max_iter) return alpha;
-    if (val_der >= 0) {
-      a_val = val, a_val_der = val_der, b_val = last_val, b_val_der = last_val_der;
-      a = alpha, b = last_alpha;
+    if (fabs(cur.slope) <= flat) return cur.step;
+    if (prev.step == cur.step || evals >= max_evals) return cur.step;
+    if (cur.slope >= 0) {
+      lo = cur, hi = prev;
       break;
     }
-    const double temp = alpha;
-    double first, last;
-    if (mu > 0) {
-      first = fmin(mu, alpha + tau1a * (alpha - last_alpha));
-      last = fmin(mu, alpha + tau1b * (alpha - last_alpha));
-    } else {
-      first = fmax(mu, alpha + tau1a * (alpha - last_alpha));
-      last = fmax(mu, alpha + tau1b * (alpha - last_alpha));
-    }
-    if (last_alpha < alpha) {
-      alpha = last_alpha + (alpha - last_alpha) * poly_min_extrap(last_val, last_val_der, val, val_der, 1e10);
-    } else {
-      alpha = alpha + (last_alpha - alpha) * poly_min_extrap(val, val_der, last_val, last_val_der, 1e10);
-    }
-    alpha = put_in_range(first, last, alpha);
-    last_alpha = temp;
-    last_val = val;
-    last_val_der = val_der;
+    const double gap = cur.step - prev.step;
+    double nearest = cur.step + 1.4 * gap, farthest = cur.step + 9 * gap;
+    if (step_cap > 0)
+      nearest = fmin(step_cap, nearest), farthest = fmin(step_cap, farthest);
+    else
+      nearest = fmax(step_cap, nearest), farthest = fmax(step_cap, farthest);
+    const double guess =
+        (prev.step < cur.step)
+            ? prev.step + (cur.step - prev.step) * cubic_minimiser(prev.value, prev.slope, cur.value, cur.slope, 1e10)
+            : cur.step + (prev.step - cur.step) * cubic_minimiser(cur.value, cur.slope, prev.value, prev.slope, 1e10);
+    trial = put_in_range(nearest, farthest, guess);
+    prev = cur;
   }
-  while (true) {
-    ++itr;
-    const double first = a + tau2 * (b - a);
-    const double last = b - tau3 * (b - a);
-    alpha = a + (b - a) * poly_min_extrap(a_val, a_val_der, b_val, b_val_der);
-    alpha = put_in_range(first, last, alpha);
-    const double val = f(alpha);
-    const double val_der = der(alpha);
-    if (val <= min_f || itr >= max_iter) return alpha;
-    if (a == first || b == last) return b;
-    const double max_possible_alpha = fmax(fabs(a), fabs(b));
-    if (fabs(max_possible_alpha * d0) <= fabs(f0) * kEps) return alpha;
-    if (val > f0 + rho * alpha * d0 || val >= a_val) {
-      b = alpha, b_val = val, b_val_der = val_der;
+  for (;;) {  // sectioning: shrink [lo, hi] (hi may lie below lo) around a point that satisfies both conditions
+    ++evals;
+    const double width = hi.step - lo.step;
+    const double nearest = lo.step + 0.1 * width;
+    const double farthest = hi.step - 0.5 * width;
+    const Probe cur = probe(put_in_range(
+        nearest, farthest, lo.step + width * cubic_minimiser(lo.value, lo.slope, hi.value, hi.slope)));
+    if (cur.value <= floor_value || evals >= max_evals) return cur.step;
+    if (lo.step == nearest || hi.step == farthest) return hi.step;
+    const double reach = fmax(fabs(lo.step), fabs(hi.step));
+    if (fabs(reach * slope0) <= fabs(phi0) * kEps) return cur.step;
+    if (too_high(cur) || cur.value >= lo.value) {
+      hi = cur;
     } else {
-      if (fabs(val_der) <= thresh) return alpha;
-      if ((b - a) * val_der >= 0) b = a, b_val = a_val, b_val_der = a_val_der;
-      a = alpha, a_val = val, a_val_der = val_der;
+      if (fabs(cur.slope) <= flat) return cur.step;
+      if ((hi.step - lo.step) * cur.slope >= 0) hi = lo;
+      lo = cur;
     }
   }
 }
@@ -133,7 +136,7 @@ struct Lbfgs {
   int size = 0;
   V2 prev_x{0, 0}, prev_der{0, 0}, dir{0, 0};
 
-  __device__ V2 next_direction(const V2& x, const V2& g) {
+  MB200_HD V2 next_direction(const V2& x, const V2& g) {
     dir = neg(g);
     if (!been_used) {
       been_used = true;
@@ -176,7 +179,7 @@ struct Lbfgs {
 // position, which is min_allowable_cost; the stop strategy keeps its default objective delta of 1e-7 and the derivative
 // step its default 1e-7 (PointEllipsoid.hpp:118-119, EllipsoidEllipsoid.hpp:139-140, Circle3DCircle3D.hpp:140-141).
 template <class Cost>
-__device__ inline double find_min(const Cost& cost_func, V2& x, double min_allowable_cost) {
+MB200_HD inline double find_min(const Cost& cost_func, V2& x, double min_allowable_cost) {
   const double eps = 1e-7, min_delta = 1e-7;
   auto grad = [&](const V2& p) {  // central_differences, :190-211
     V2 der;
@@ -222,7 +225,7 @@ struct Ellipsoid {
 };
 
 // mundy/geom/src/mundy_geom/primitives/Ellipsoid.hpp:418-468
-__device__ inline V3 body_normal_to_ellipsoid(const V3& nb, const Ellipsoid& e) {
+MB200_HD inline V3 body_normal_to_ellipsoid(const V3& nb, const Ellipsoid& e) {
   const double r1 = e.rad.x, r2 = e.rad.y, r3 = e.rad.z;
   const double sign0 = copysign(1.0, nb.x), sign1 = copysign(1.0, nb.y), sign2 = copysign(1.0, nb.z);
   double alpha1, alpha2;
@@ -246,17 +249,17 @@ __device__ inline V3 body_normal_to_ellipsoid(const V3& nb, const Ellipsoid& e) 
   const double z = 0.5 * sign2 * ((1.0 + sign2) * r3 + (1.0 - sign2) * r3) * sqrt(1.0 - alpha2);
   return {x, y, z};
 }
-__device__ inline V3 normal_to_foot_point(const V3& n, const Ellipsoid& e) {
+MB200_HD inline V3 normal_to_foot_point(const V3& n, const Ellipsoid& e) {
   const V3 nb = qrot(qconj(e.q), n);
   return qrot(e.q, body_normal_to_ellipsoid(nb, e)) + e.c;
 }
-__device__ inline V3 angles_to_normal(const V2& tp) {
+MB200_HD inline V3 angles_to_normal(const V2& tp) {
   const double st = sin(tp.a), ct = cos(tp.a), sp = sin(tp.b), cp = cos(tp.b);
   return {st * cp, st * sp, ct};
 }
 
 // PointEllipsoid.hpp:97-135
-__device__ inline double dist_point_ellipsoid(const V3& x, const Ellipsoid& e, V3& cp, V3& normal) {
+MB200_HD inline double dist_point_ellipsoid(const V3& x, const Ellipsoid& e, V3& cp, V3& normal) {
   auto obj = [&](const V2& tp) {
     const V3 n = angles_to_normal(tp);
     V3 sep;
@@ -279,7 +282,7 @@ __device__ inline double dist_point_ellipsoid(const V3& x, const Ellipsoid& e, V
 }
 
 // EllipsoidEllipsoid.hpp:109-151
-__device__ inline double dist_ellipsoid_ellipsoid(const Ellipsoid& e1, const Ellipsoid& e2, V3& cp1, V3& cp2, V3& n1) {
+MB200_HD inline double dist_ellipsoid_ellipsoid(const Ellipsoid& e1, const Ellipsoid& e2, V3& cp1, V3& cp2, V3& n1) {
   auto obj = [&](const V2& tp) {
     const V3 n = angles_to_normal(tp);
     const V3 m{-n.x, -n.y, -n.z};
@@ -309,12 +312,12 @@ struct Circle {
   double r;
 };
 // Circle3DCircle3D.hpp:81-86
-__device__ inline V3 circle_point(double theta, const Circle& k) {
+MB200_HD inline V3 circle_point(double theta, const Circle& k) {
   const V3 pl{k.r * cos(theta), k.r * sin(theta), 0.0};
   return qrot(k.q, pl) + k.c;
 }
 // Circle3DCircle3D.hpp:88-151 (Euclidean)
-__device__ inline double dist_circle_circle(const Circle& k1, const Circle& k2, V3& cp1, V3& cp2, V3& n1) {
+MB200_HD inline double dist_circle_circle(const Circle& k1, const Circle& k2, V3& cp1, V3& cp2, V3& n1) {
   auto obj = [&](const V2& tt) {
     V3 sep;
     return dist_pp(circle_point(tt.a, k1), circle_point(tt.b, k2), sep);

@@ -96,3 +96,37 @@ def test_circle_distance_is_a_minimum_over_a_dense_scan():
         scan = np.min(np.linalg.norm(A[:, None, :] - B[None, :, :], axis=2))
         assert dist[i] <= scan + 1e-6 and dist[i] >= scan - 2e-2   # the scan's grid is 0.5 degrees
         assert abs(np.linalg.norm(cp2[i] - cp1[i]) - dist[i]) < 1e-12
+
+
+# ---- the product's own minimiser source, instantiated on the host -----------------------------------------------------
+def _host_harness():
+    """tests/cpp/host_minimize_check.cu: mundy_b200/csrc/minimize.cuh (the text the device kernels are compiled from,
+    __host__ __device__) compiled for the HOST by nvcc with contraction off, behind the oracle's calling convention."""
+    import ctypes
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available")
+    src = os.path.join(root, "tests", "cpp", "host_minimize_check.cu")
+    hdr = os.path.join(root, "mundy_b200", "csrc", "minimize.cuh")
+    out = os.path.join(root, "build", "libhost_minimize_check.so")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O2", "-fmad=false", "-Xcompiler", "-fPIC",
+               "-Xcompiler", "-ffp-contract=off", "-shared", "-I", os.path.join(root, "include"), "-I",
+               os.path.join(root, "mundy_b200", "csrc"), src, "-o", out, "-cudart", "static"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    return ctypes.CDLL(out)
+
+
+@pytest.mark.parametrize("name", ["point_ellipsoid", "ellipsoid_ellipsoid", "circle_circle"])
+def test_product_minimiser_source_on_the_host_matches_reference_bit_for_bit(name):
+    """The device code path cannot be bit-exact (CUDA's sin / cos); the SOURCE is: compiled for the host, where sin / cos
+    are glibc's like the reference's, it reproduces the reference's stored outputs exactly."""
+    lib = _host_harness()
+    got = _tuple(oracle.primitive(name, *_ins(name), lib=lib, prefix="hostchk_"))
+    for k, g in enumerate(got):
+        assert np.array_equal(g, G[f"{name}.out{k}"]), (name, k)
