@@ -128,6 +128,7 @@ __global__ void __launch_bounds__(256) cell_ranges_kernel(int64_t n, const uint3
 // first test, exact fp64 predicate, warp ballot + popc compaction.
 // PER: periodic box. Neighbour cells wrap around on periodic axes (an axis with fewer than three cells visits each of
 // its cells once), the predicate uses the minimum-image separation and the shape filter unwraps the second body.
+constexpr int kFindGroup = 8;  // consecutive bodies per warp in find_pairs_kernel
 #ifndef MB200_FIND_MIN_CTAS
 #define MB200_FIND_MIN_CTAS 4  // 64 registers: four CTAs (32 warps) per SM; measured 4.70 / 3.98 / 3.67 ms per rebuild at 2 / 3 / 4
 #endif
@@ -140,16 +141,29 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
                       const uint8_t* __restrict__ own, Periodic P) {
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
-  const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-  if (i >= n) return;
+  // A warp takes kFindGroup consecutive bodies. Consecutive bodies mostly share their cell, and with it the neighbour
+  // cells, their ranks and prefixes: that set-up (27 cell keys and ranges, 54 shuffles) is redone only when the cell
+  // changes. Inside a cell only the own cell's range [i + 1, end) moves: every later prefix shrinks by i - base_i.
+  const int64_t i_begin = ((static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5) * kFindGroup;
+  if (i_begin >= n) return;
+  const int64_t i_end = min(n, i_begin + kFindGroup);
   const uint32_t lt_mask = (1u << lane) - 1u;
+  __shared__ int s_pre[8][28], s_beg[8][28];
+  __shared__ int s_queue[FILTER ? 8 : 1][FILTER ? 96 : 1];
+  const int* wpre = s_pre[wib];
+  const int* wbeg = s_beg[wib];
+  int* q = s_queue[FILTER ? wib : 0];
+  uint32_t cur_key = 0xffffffffu;
+  int64_t base_i = 0;
+  int nvalid = 0, total_base = 0, rpre_base = 0x7fffffff;
+  for (int64_t i = i_begin; i < i_end; ++i) {
   int64_t out = FILL ? rowptr[i] : 0;
   if (FILL) {
     const int cnt = static_cast<int>(rowptr[i + 1] - out);
     if (cnt <= slot_cap) {  // everything was cached by the count pass
       for (int k = lane; k < cnt; k += 32)
         pairs[out + k] = make_int2(static_cast<int>(i), slots[i * slot_cap + k]);
-      return;
+      continue;
     }
   }
   const D4 si = ldg256(sr + i);
@@ -161,6 +175,7 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
   const int cy = cell_coord(si.y, gp, 1);
   const int cz = cell_coord(si.z, gp, 2);
   const uint32_t my_key = morton3(cx, cy, cz);
+  if (my_key != cur_key) {
   // lane l < 27 owns neighbour cell l
   uint32_t nkey = 0xffffffffu;
   int beg = 0, len = 0;
@@ -185,7 +200,10 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
         const int2 r = __ldg(cell_range + k);
         beg = (k == my_key) ? static_cast<int>(i) + 1 : r.x;
         len = r.y - beg;
-        if (len > 0) nkey = k; else len = 0;
+        // the own cell (smallest key: rank 0) stays in the table even when i is its last body, so that the bodies that
+        // reuse this table find it at rank 0
+        if (len > 0 || k == my_key) nkey = k;
+        if (len < 0) len = 0;
       }
     }
   }
@@ -201,35 +219,41 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
       pre += lm;
     }
   }
-  const int nvalid = __popc(__ballot_sync(0xffffffffu, valid));
-  __shared__ int s_pre[8][28], s_beg[8][28];
-  __shared__ int s_queue[FILTER ? 8 : 1][FILTER ? 96 : 1];
+  nvalid = __popc(__ballot_sync(0xffffffffu, valid));
+  __syncwarp();  // the previous table is no longer read
   if (valid) {
     s_pre[wib][rank] = pre;
     s_beg[wib][rank] = beg;
   }
-  int total_cand = valid ? pre + len : 0;
+  int tc = valid ? pre + len : 0;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) total_cand = max(total_cand, __shfl_xor_sync(0xffffffffu, total_cand, o));
+  for (int o = 16; o > 0; o >>= 1) tc = max(tc, __shfl_xor_sync(0xffffffffu, tc, o));
   __syncwarp();
-  const int* wpre = s_pre[wib];
-  const int* wbeg = s_beg[wib];
+  total_base = tc;
+  rpre_base = (lane < nvalid) ? wpre[lane] : 0x7fffffff;
+  cur_key = my_key;
+  base_i = i;
+  }
+  // this body against the table of base_i (same cell): the own cell starts delta later and is delta shorter
+  const int delta = static_cast<int>(i - base_i);
+  const int total_cand = total_base - delta;
   // flattened index tb0 + lane -> body index. Lane r keeps the prefix of the cell of rank r; the cells that start inside
   // a batch of 32 consecutive indices are marked in one warp-wide OR, so a lane finds its cell with two population counts
-  // instead of a binary search through shared memory.
-  const int rpre = (lane < nvalid) ? wpre[lane] : 0x7fffffff;
+  // instead of a binary search through shared memory. (An emptied own cell shares prefix 0 with rank 1 and is skipped.)
+  const int rpre = (lane == 0) ? 0 : ((lane < nvalid) ? rpre_base - delta : 0x7fffffff);
   auto candidate = [&](int tb0) {
     const uint32_t below = __ballot_sync(0xffffffffu, rpre <= tb0);  // rank 0 starts at 0: never empty
     const int rel = rpre - tb0;
     const uint32_t starts = __reduce_or_sync(0xffffffffu, (rel > 0 && rel < 32) ? (1u << rel) : 0u);
     const int lo = __popc(below) - 1 + __popc(starts & ((2u << lane) - 1u));
-    return wbeg[lo] + (tb0 + lane - wpre[lo]);
+    const int pre_lo = (lo == 0) ? 0 : wpre[lo] - delta;
+    const int beg_lo = (lo == 0) ? static_cast<int>(i) + 1 : wbeg[lo];
+    return beg_lo + (tb0 + lane - pre_lo);
   };
 
   uint32_t total = 0;
   // With the shape filter the survivors of the sphere test (about 1 in 10) are queued per warp and the expensive
   // shape distance runs on dense batches of 32, in queue order (= ascending j), instead of on a few divergent lanes.
-  int* q = s_queue[FILTER ? wib : 0];
   int qn = 0;
   auto emit = [&](bool keep, int j) {
     const uint32_t m = __ballot_sync(0xffffffffu, keep);
@@ -289,6 +313,7 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
     }
   }
   if (!FILL && lane == 0) counts[i] = total;
+  }
 }
 
 }  // namespace
@@ -463,7 +488,7 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   MB200_TRY(counts.alloc(n, st));
   MB200_TRY(rowptr.alloc(n + 1, st));
   const double cutoff = 2.0 * h->buffer;
-  const int pgrid = grid_for(n * 32, 256);
+  const int pgrid = grid_for(((n + kFindGroup - 1) / kFindGroup) * 32, 256);
   auto launch_find = [&](auto fill_tag, const int64_t* rp, int2* out) {
     constexpr bool FILL = decltype(fill_tag)::value;
     uint32_t* cnt = FILL ? nullptr : counts.p;

@@ -91,7 +91,14 @@ struct Scratch {
     st = s;
     count = n;
     if (n == 0) return MB200_OK;
-    MB200_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&p), n * sizeof(T), s));
+    // Sizes are rounded up to a granule of about 1/32 of the request (at least 64 KB): the per-step scratch sizes follow
+    // the contact count, which moves by a few parts in 10^4 from step to step, and the stream-ordered pool can only
+    // reuse a cached block that is large enough. With repeating sizes it never has to map new memory mid-run.
+    size_t bytes = n * sizeof(T);
+    size_t granule = size_t(64) << 10;
+    while (granule * 32 < bytes) granule <<= 1;
+    bytes = (bytes + granule - 1) / granule * granule;
+    MB200_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&p), bytes, s));
     return MB200_OK;
   }
   void release() {
