@@ -3,7 +3,7 @@
 //
 //   search spheres {c, S}  ->  Morton key of the uniform-grid cell (edge >= 2 S_max)  ->  radix sort (key, body)
 //   -> bodies gathered into Morton order (32-byte records)  ->  dense cell table [start, end)
-//   -> one warp per body walks its <= 27 neighbour cells in ascending key order, 32 candidates per step read as one
+//   -> a warp walks each body's <= 27 neighbour cells in ascending key order, 32 candidates per step read as one
 //      contiguous run of records, exact fp64 predicate, warp ballot + popc compaction
 //   -> count pass, exclusive scan, fill pass: pair list sorted by (i, j) in Morton-order indices, no atomics.
 // The optional shape-distance search filter (GenNeighborLinkers.hpp:116-200 SearchFilter) is fused into the same passes.
@@ -118,7 +118,8 @@ __global__ void __launch_bounds__(256) cell_ranges_kernel(int64_t n, const uint3
   if (k == n - 1 || keys[k + 1] != key) cell_range[key].y = static_cast<int>(k + 1);
 }
 
-// One warp per body i (Morton order).
+// One warp per kFindGroup consecutive bodies (Morton order), one body at a time; the per-cell table (neighbour cells,
+// ranks, prefixes) is shared by the bodies of a cell.
 //   FILL = false: counts[i] = number of kept pairs (i, j>i); the first `slot_cap` of them are also cached in
 //                 slots[i * slot_cap ...] so that the fill pass does not have to search again.
 //   FILL = true : writes the pairs at pairs[rowptr[i] ...] in ascending j: copied from the slots when they all fit,
