@@ -148,6 +148,15 @@ inline void parallel_reduce(const std::string&, const Policy& p, const F& f, Max
   red.ref = acc;
 }
 
+// Three-Sum-reducer form (scrap/lcp_spheres/KokkosLCP.cpp:536-556). Serial and in index order: the only caller is the
+// driver-LCP pin (oracle/ref_lcp.cpp), which wants the Kokkos Serial backend's order.
+template <class Policy, class F, class T>
+inline void parallel_reduce(const std::string&, const Policy& p, const F& f, Sum<T> r0, Sum<T> r1, Sum<T> r2) {
+  T a0 = 0, a1 = 0, a2 = 0;
+  for (long i = static_cast<long>(p.begin); i < static_cast<long>(p.end); ++i) f(static_cast<int>(i), a0, a1, a2);
+  r0.ref = a0, r1.ref = a1, r2.ref = a2;
+}
+
 }  // namespace Kokkos
 
 namespace KokkosBlas {

@@ -448,3 +448,95 @@ def solve_contact_lcp_convex(n, pairs, normal, r, mu, dt, phi0, gamma0, max_iter
     conv = fn(C.byref(ctx), _p(_a(phi0)), _p(gamma), C.c_uint(max_iters), C.c_double(tol), C.c_int(resid_kind),
               C.byref(iters), C.byref(resid))
     return dict(x=gamma, iters=iters.value, residual=resid.value, converged=bool(conv))
+
+
+# ---- driver LCP: summation order of the oracle, and the reference's own function bodies (oracle/ref_lcp.cpp) -----------
+SUM_CHUNKS, SUM_SERIAL, SUM_DEVICE = 0, 1, 2
+
+
+def set_sum_order(mode, grid=1, threads=256):
+    """Order of the three Barzilai-Borwein sums inside oracle.resolve_collisions (see bb_sums in the oracle source):
+    SUM_CHUNKS (default), SUM_SERIAL (= Kokkos Serial backend = oracle/_ref), SUM_DEVICE (= the rate pass's tree)."""
+    _call(orc, "orc_set_sum_order", int(mode), int(grid), int(threads))
+
+
+class sum_order:
+    """with oracle.sum_order(oracle.SUM_SERIAL): ..."""
+
+    def __init__(self, mode, grid=1, threads=256):
+        self.args = (mode, grid, threads)
+
+    def __enter__(self):
+        set_sum_order(*self.args)
+
+    def __exit__(self, *exc):
+        set_sum_order(SUM_CHUNKS)
+
+
+def diff_dots(x, xp, g, gp, dt):
+    out = np.empty(3)
+    _call(orc, "orc_diff_dots", len(x), _a(x), _a(xp), _a(g), _a(gp), float(dt), out)
+    return out
+
+
+def max_abs_projected_sep(gamma, phi0, gdot, dt):
+    return _call(orc, "orc_max_abs_projected_sep", len(gamma), _a(gamma), _a(phi0), _a(gdot), float(dt),
+                 restype=C.c_double)
+
+
+# The reference's own kernels, scrap/lcp_spheres/KokkosLCP.cpp:449-876 (monodisperse spheres, dry mobility)
+def ref_lcp_narrow(ids, radius, pos):
+    ids = _a(ids, _i)
+    sep, normal = np.empty(len(ids)), np.empty((len(ids), 3))
+    _call(ref, "ref_lcp_signed_sep_and_normal", len(pos), len(ids), ids, float(radius), _a(pos), sep, normal)
+    return sep, normal
+
+
+def ref_lcp_D(n, ids, normal, gamma):
+    F = np.empty((n, 3))
+    _call(ref, "ref_lcp_sum_collision_force", n, len(ids), _a(ids, _i), _a(normal), _a(gamma), F)
+    return F
+
+
+def ref_lcp_M(radius, mu, F):
+    U = np.zeros_like(_a(F))
+    _call(ref, "ref_lcp_mobility", len(F), float(radius), float(mu), _a(F), U)
+    return U
+
+
+def ref_lcp_DT(n, ids, normal, U):
+    g = np.empty(len(ids))
+    _call(ref, "ref_lcp_rate_of_change_of_sep", n, len(ids), _a(ids, _i), _a(normal), _a(U), g)
+    return g
+
+
+def ref_lcp_residual(gamma, sep, sep_dot, dt):
+    return _call(ref, "ref_lcp_max_abs_projected_sep", len(gamma), _a(gamma), _a(sep), _a(sep_dot), float(dt),
+                 restype=C.c_double)
+
+
+def ref_lcp_diff_dots(x, xp, g, gp, dt):
+    out = np.empty(3)
+    _call(ref, "ref_lcp_diff_dots", len(x), _a(x), _a(xp), _a(g), _a(gp), float(dt), out)
+    return out
+
+
+def ref_lcp_update_gammas(gamma_tmp, sep, sep_dot, dt, alpha):
+    gamma = np.empty(len(gamma_tmp))
+    _call(ref, "ref_lcp_update_con_gammas", len(gamma), gamma, _a(gamma_tmp), _a(sep), _a(sep_dot), float(dt),
+          float(alpha))
+    return gamma
+
+
+def ref_lcp_resolve(ids, radius, mu, dt, tol, max_it, pos, sep, normal, gamma0=None):
+    """resolve_collisions of KokkosLCP.cpp:675-876 (enable_hydro = false). A fixed iteration count K is (tol=0, max_it=K)."""
+    ids = _a(ids, _i)
+    n, m = len(pos), len(ids)
+    gamma = np.zeros(m) if gamma0 is None else _a(gamma0).copy()
+    F, U = np.zeros((n, 3)), np.zeros((n, 3))
+    res = CollisionResult()
+    fn = ref.ref_lcp_resolve_collisions
+    fn.restype = None
+    fn(C.c_long(n), C.c_long(m), _p(ids), C.c_double(radius), C.c_double(mu), C.c_double(dt), C.c_double(tol),
+       C.c_int(max_it), _p(_a(pos)), _p(_a(sep)), _p(_a(normal)), _p(gamma), _p(F), _p(U), C.byref(res))
+    return dict(res=res.max_abs_projected_sep, it=res.ite_count, max_disp=res.max_displacement, gamma=gamma, F=F, U=U)
