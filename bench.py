@@ -10,11 +10,14 @@ in a cube at volume fraction 0.10, driver parameters mu = 1e-3, dt = 1e-4, searc
 
   value  particle-timesteps/s with the bodies resident in HBM (device entry point mb200_collision_step)
   e2e    the same through mb200_collision_step_host: pinned HOST arrays in, H2D + step + D2H inside the timed region
-  roofline   dominant kernel (the BBPGD rate pass): algorithmic bytes / CUDA-event time of its launches in the timed
-             region, against MEASURED_PEAKS.json hbm_gbs
-  cpu_baseline   the CPU oracle step (OpenMP restatement of the reference loop, "port") on a bounded sample
+  roofline   the dominant kernel group = one BBPGD iteration (body pass + rate pass): SURVEY.md 8(d)'s algorithmic bytes
+             (120 C + 240 N for rods) / CUDA-event time of the two launches in the timed region, against
+             MEASURED_PEAKS.json hbm_gbs; `stages` carries the 8(d) bytes and fraction of every other stage
+  cpu_baseline   the CPU oracle step (OpenMP restatement of the reference loop, "port", pinned bit for bit to the
+             reference's own code compiled in oracle/_ref) on a bounded sample, all host threads
 
-`--impl reference` times that CPU implementation alone (rank 0 only under torchrun).
+`--impl reference` times that CPU implementation alone on the SAME workload (rank 0 only under torchrun; bodies capped
+by --cpu-cap for multi-GPU configurations so that the run ends within minutes).
 """
 import argparse
 import json
@@ -48,7 +51,10 @@ def parse_args():
     ap.add_argument("--filter", default="shape", choices=["shape", "none"],
                     help="search filter: shape-distance (default) or every bounding-sphere candidate")
     ap.add_argument("--prep", type=int, default=2, help="untimed steps that relax the random initial overlaps")
-    ap.add_argument("--cpu-bodies", type=int, default=100_000, help="bodies of the CPU sample")
+    ap.add_argument("--cpu-bodies", type=int, default=100_000, help="bodies of the in-line cpu_baseline sample")
+    ap.add_argument("--cpu-cap", type=int, default=1_000_000,
+                    help="--impl reference: at most this many bodies (the one-GPU workload); larger multi-GPU "
+                         "configurations are sampled at this size, same density and parameters")
     ap.add_argument("--cpu-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -130,8 +136,10 @@ class ClockSampler:
 def cpu_steps(n, steps, warmup, filt, seed=3):
     """Times `steps` oracle collision steps on n bodies after `warmup` untimed ones. Returns (seconds, info)."""
     import numpy as np  # noqa: F401
+    use_all_host_threads()  # before the oracle (and with it libgomp) is loaded
     import oracle
-    from mundy_b200 import workloads as wl
+    wl = load_workloads()
+    use_all_host_threads()
 
     w = wl.rods(n, phi=PHI, radius=RADIUS, length=LENGTH, seed=seed)
     state, links = (w["center"].copy(), w["quat"].copy()), None
@@ -159,38 +167,86 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+# taken at import: with OMP_PROC_BIND set, libgomp pins the main thread to one place when it loads, after which the
+# affinity mask of this process no longer says how many cores it may use
+_HOST_THREADS = host_threads()
+
+
+def use_all_host_threads():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU arm is meant to use every host core the
+    process may run on. Sets the environment (read by libgomp when the oracle loads it) and, once it is loaded, the
+    runtime itself."""
+    import ctypes
+    n = _HOST_THREADS
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    os.environ.setdefault("OMP_PROC_BIND", "spread")  # the reference's own job template (mundy_brownian_*.run.in)
+    os.environ.setdefault("OMP_PLACES", "threads")
+    try:
+        ctypes.CDLL("libgomp.so.1", mode=ctypes.RTLD_GLOBAL).omp_set_num_threads(n)
+    except (OSError, AttributeError):
+        pass
+    return n
+
+
+def omp_threads_in_use():
+    import ctypes
+    try:
+        return int(ctypes.CDLL("libgomp.so.1").omp_get_max_threads())
+    except (OSError, AttributeError):
+        return 1
+
+
+def load_workloads():
+    """mundy_b200/workloads.py by path: importing the package would map libmundy_b200.so into the CPU arm."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("mb200_workloads", os.path.join(ROOT, "mundy_b200", "workloads.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n = args.cpu_bodies
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    n_cfg = args.bodies * max(world, 1)          # the B200 arm's workload: `bodies` per GPU in one box
+    n = min(n_cfg, args.cpu_cap)
     filt = args.filter == "shape"
     secs, info = cpu_steps(n, args.steps, max(args.warmup, 1), filt)
     value = n * args.steps / secs
-    cores = int(os.environ.get("OMP_NUM_THREADS", host_threads()))
-    sample = (f"{n} spherocylinders (same density/parameters as the 10^6 workload), {args.steps} steps after "
-              f"{max(args.warmup, 1)} warm-up steps, OpenMP oracle step")
+    cores = omp_threads_in_use()
+    sample = (f"{n} spherocylinders, {args.steps} steps after {max(args.warmup, 1)} warm-up steps, OpenMP oracle step on "
+              f"{cores} threads" + ("" if n == n_cfg else f" (sample of the {n_cfg}-body configuration: same density and "
+                                                          "parameters, bodies capped by --cpu-cap)"))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, n),
+        "config": workload_config(args, args.bodies, world),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "lcp_iters_per_step": info["iters_per_step"], "links": info["links"],
+        "same_config": n == n_cfg, "bodies": n,
     }
     emit(line)
 
 
-def workload_config(args, n):
+def workload_config(args, n, world, exchange=None):
+    if world == 1:
+        par = "1 GPU"
+    else:
+        how = {"peer": "velocity halo stored into the peers' arenas by the body pass and solver sums reduced inside the "
+                       "rate pass over peer memory (NVLink)",
+               "nccl": "velocity halo by NCCL send/recv and solver sums by NCCL all-gather, per iteration"}.get(exchange)
+        par = (f"{world} ranks, one box of {world}x{n} bodies, Hilbert-curve blocks"
+               + (f"; {how}; state all-gather per step" if how else ""))
     return {"workload": f"{n} spherocylinders/GPU, aspect ratio 10 (r=0.5, L=9), volume fraction {PHI}, uniform random "
                         "(BASELINE.json configs[2])",
             "bodies_per_gpu": n, "mu": MU, "dt": DT, "tol": TOL, "max_iters": MAX_ITERS, "search_buffer": BUFFER,
             "search_filter": "shape_distance<=2*buffer" if args.filter == "shape" else "none (all bounding-sphere candidates)",
-            "forcing": "attractive ABC flow", "l2": "inputs larger than L2 (contact arrays >= 400 MB per GPU)",
-            "parallelism": "1 GPU" if args.gpus == 1 else
-            f"{args.gpus} ranks, one box of {args.gpus}x{n} bodies, Hilbert-curve blocks, ghost velocity halo (NCCL send/recv) "
-            "+ all-gathered solver sums per iteration, state all-gather per step"}
+            "forcing": "attractive ABC flow", "l2": "inputs larger than L2 (contact arrays >= 250 MB per GPU)",
+            "parallelism": par}
 
 
 # ---- B200 arm ---------------------------------------------------------------------------------------------------------
@@ -373,53 +429,64 @@ def run_b200(args):
     roofline = None
     stage_out = {}
     if stages:
-        # algorithmic bytes per launch (DESIGN.md "Kernels"): C contacts, n bodies, 6-DOF
+        # Algorithmic bytes per launch = SURVEY.md 8(d)'s per-unit figures (C contacts, N bodies, rods):
+        #   rebuild 32 N + 64 N + 8 C | trigger 48 N | narrow phase 88 C + 72 N | Euler 72 N + 88 N
+        #   one BBPGD iteration 120 C + 240 N, which the two kernels of an iteration share: the per-kernel entries carry
+        #   the bytes this implementation's layout needs, the iteration carries 8(d)'s.
         nloc = mbd.local_counts(links)[0] if comm is not None else n  # bodies this rank works on (owned + ghosts)
-        alg = {"lcp_rate": 128.0 * C + 64.0 * nloc, "lcp_body": 120.0 * C + 104.0 * nloc}
+        alg = {"broadphase": 96.0 * nloc + 8.0 * C, "trigger": 48.0 * nloc, "narrow": 88.0 * C + 72.0 * nloc,
+               "euler": 160.0 * nloc,
+               "lcp_rate": 88.0 * C + 64.0 * nloc,   # state 16 r + 16 w, {n, phi0} 32, sigma 16, ids 8; velocity records once
+               "lcp_body": 32.0 * C + 176.0 * nloc}  # 8(d) iteration bytes minus the rate pass's
         for name, (tot_ms, cnt) in stages.items():
             stage_out[name] = {"ms_total": round(tot_ms, 4), "regions": cnt, "calls": stage_calls.get(name, cnt)}
             if name in alg and cnt > 0:
                 gbs = alg[name] / (tot_ms / cnt * 1e-3) / 1e9
-                stage_out[name].update({"alg_bytes": alg[name], "gbs": round(gbs, 1), "frac": round(gbs / peak, 4)})
-        dom = max(("lcp_rate", "lcp_body"), key=lambda k: stages[k][0])
-        tot_ms, cnt = stages[dom]
-        if cnt > 0:
-            achieved = alg[dom] / (tot_ms / cnt * 1e-3) / 1e9
-            traffic = None  # DRAM bytes per launch from the committed ncu capture (same workload), if there is one
+                stage_out[name].update({"avg_us": round(1e3 * tot_ms / cnt, 2), "alg_bytes": alg[name],
+                                        "gbs": round(gbs, 1), "frac": round(gbs / peak, 4)})
+        if stages["lcp_rate"][1] > 0 and stages["lcp_body"][1] > 0:
+            # one operator application = one body pass + one rate pass: the dominant kernel group of the step
+            it_ms = sum(stages[k][0] / stages[k][1] for k in ("lcp_rate", "lcp_body"))
+            it_bytes = 120.0 * C + 240.0 * nloc
+            achieved = it_bytes / (it_ms * 1e-3) / 1e9
+            calls = stage_calls.get("lcp_rate", 0)
+            traffic = None  # DRAM bytes per iteration (body + rate) from the committed ncu capture of this workload
             try:
                 if n == 1_000_000 and args.filter == "shape":
-                    traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(dom)
-            except (OSError, ValueError):
+                    tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+                    traffic = tj.get("lcp_body", 0) + tj.get("lcp_rate", 0) or None
+            except (OSError, ValueError, TypeError):
                 pass
-            roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                        "launches": stage_calls.get(dom, cnt), "launches_timed": cnt, "avg_us": 1e3 * tot_ms / cnt,
-                        "share_of_step": (tot_ms / cnt) * stage_calls.get(dom, cnt) / ms,
+            roofline = {"bound": "hbm", "kernel": "lcp_iteration (body_pass_kernel + rate_pass_kernel)",
+                        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                        "alg_bytes": it_bytes, "alg_bytes_model": "SURVEY.md 8(d): 120 C + 240 N per rod iteration",
+                        "peak_source": peak_src, "launches": 2 * calls,
+                        "launches_timed": stages["lcp_rate"][1] + stages["lcp_body"][1], "avg_us": 1e3 * it_ms,
+                        "share_of_step": it_ms * calls / ms,
+                        "body_pass_us": 1e3 * stages["lcp_body"][0] / stages["lcp_body"][1],
+                        "rate_pass_us": 1e3 * stages["lcp_rate"][0] / stages["lcp_rate"][1],
                         "timing": f"CUDA events around every {max(1, args.stage_sample)}-th launch inside the timed region"}
-            if stages["lcp_rate"][1] > 0 and stages["lcp_body"][1] > 0:
-                # one operator application = one body pass + one contact pass
-                it_ms = sum(stages[k][0] / stages[k][1] for k in ("lcp_rate", "lcp_body"))
-                it_bytes = 120.0 * C + 240.0 * nloc  # fused-ideal bytes of one rod BBPGD iteration
-                roofline["lcp_iteration"] = {"alg_bytes": it_bytes, "avg_us": 1e3 * it_ms,
-                                             "gbs": it_bytes / (it_ms * 1e-3) / 1e9,
-                                             "frac": it_bytes / (it_ms * 1e-3) / 1e9 / peak}
 
     cpu = None
     if not args.no_cpu_baseline:
         secs, info = cpu_steps(args.cpu_bodies, args.cpu_steps, 1, filt)
-        cpu = {"value": args.cpu_bodies * args.cpu_steps / secs, "unit": UNIT,
-               "cores": int(os.environ.get("OMP_NUM_THREADS", host_threads())), "kind": "port",
+        cpu = {"value": args.cpu_bodies * args.cpu_steps / secs, "unit": UNIT, "cores": omp_threads_in_use(), "kind": "port",
                "sample": f"{args.cpu_bodies} spherocylinders at the same density/parameters, {args.cpu_steps} steps after 1 "
                          f"warm-up step; OpenMP oracle step (LCP iterations/step {info['iters_per_step']})"}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic", "config": workload_config(args, n),
+        "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, n, world, comm.exchange_mode if comm is not None else None),
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "lcp_iters_per_step": [x[0] for x in tlog], "ms_steps": ms_steps, "links_per_step": int(C), "rebuilds": sum(x[2] for x in tlog),
         "all_converged": all(x[3] for x in tlog), "stages": stage_out, "prep_steps": args.prep,
+        "lcp_iters_mean": statistics.mean(x[0] for x in tlog),
+        "us_per_lcp_iteration": (roofline or {}).get("avg_us"),
     }
+    if args.filter != "shape":
+        line["metric"] = METRIC + " (search_filter: none, every bounding-sphere candidate is a constraint)"
     if comm is not None:
         nl, ng = mbd.local_counts(links)
         line["dist"] = {"rank0_local_bodies": nl, "rank0_ghost_rows": ng, "owned_per_rank": n,

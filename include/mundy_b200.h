@@ -292,6 +292,23 @@ int mb200_resolve_collisions(mb200_stream stream, const mb200_contact_op* op, co
                              const double* U_ext, const double* W_ext, double* phi0, double* gamma, double* F,
                              double* T, double* U, double* W, mb200_collision_result* result_h);
 
+/* The same solve with the lever arms in AXIAL form, the form mb200_collision_step runs for spherocylinders: the contact
+ * point of a rod lies on its centre line, so arm = sigma * h with h = (L/2) (q (x) z_hat) the half-axis vector of the body
+ * (compute_aabb.hpp:115-117) and sigma = 2 clamp(s, 0, 1) - 1, s = the segment parameter geom::distance returns
+ * (LineSegmentLineSegment.hpp:313-316); sigma = 0 for a sphere. sigma[2*npairs] = (sigma_i, sigma_j) per contact,
+ * length[n]; op->quat and op->kind are required, op->arm_i / arm_j must be NULL. 16 bytes per contact instead of 48. */
+int mb200_resolve_collisions_axial(mb200_stream stream, const mb200_contact_op* op, const double* sigma,
+                                   const double* length, const mb200_lcp_params* params, const double* U_ext,
+                                   const double* W_ext, double* phi0, double* gamma, double* F, double* T, double* U,
+                                   double* W, mb200_collision_result* result_h);
+
+/* Shape of the solver's deterministic global reductions (residual max and the three Barzilai-Borwein sums,
+ * KokkosLCP.cpp:493-557) for a system of npairs contacts: `grid` CTAs of `threads` threads walk the contacts with a grid
+ * stride, sum per thread, then through a shuffle tree per warp and per CTA; the CTA partials are reduced the same way.
+ * A CPU checker that adds in this order reproduces the device's iterates bit for bit at any iteration count.
+ * arm_mode: 0 no arms (3-DOF), 1 axial arms (the collision step's spherocylinders), 2 caller-supplied arm vectors. */
+int mb200_lcp_reduction_shape(int64_t npairs, int arm_mode, int32_t* grid_h, int32_t* threads_h);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * E2. math::convex projected-gradient solver  mundy/math/src/mundy_math/convex.hpp
  * ------------------------------------------------------------------------------------------------------------- */

@@ -121,6 +121,9 @@ SIGNATURES = {
     "mb200_apply_M": (C.c_int, [vp, P(ContactOp), vp, vp, vp, vp]),
     "mb200_apply_DT": (C.c_int, [vp, P(ContactOp), vp, vp, vp]),
     "mb200_apply_A": (C.c_int, [vp, P(ContactOp), vp, vp]),
+    "mb200_resolve_collisions_axial": (C.c_int, [vp, P(ContactOp), vp, vp, P(LcpParams), vp, vp, vp, vp, vp, vp, vp, vp,
+                                                P(CollisionResult)]),
+    "mb200_lcp_reduction_shape": (C.c_int, [c_i64, C.c_int, P(c_i32), P(c_i32)]),
     "mb200_resolve_collisions": (C.c_int, [vp, P(ContactOp), P(LcpParams), vp, vp, vp, vp, vp, vp, vp, vp,
                                            P(CollisionResult)]),
     "mb200_mobility_kernel_apply": (C.c_int, [vp, C.c_int, c_i64, c_i64, c_dbl, vp, vp, vp, vp, vp, vp]),

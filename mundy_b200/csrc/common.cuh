@@ -7,6 +7,7 @@
 //   q (x) v = q * (0,v) * conj(q)/|q|^2                mundy/math/src/mundy_math/impl/QuaternionImpl.hpp:142-202
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 
 #include <atomic>
@@ -56,18 +57,22 @@ inline void count_launch(int k = 1) { g_launches.fetch_add(k, std::memory_order_
 inline cudaStream_t as_stream(mb200_stream s) { return reinterpret_cast<cudaStream_t>(s); }
 
 // Stage timers (core.cu). A StageScope brackets the launches issued during its lifetime with an event pair on `st`
-// when profiling is enabled, and costs one relaxed load otherwise.
+// when profiling is enabled, and costs one relaxed load otherwise. It is also an NVTX range (header-only NVTX 3: a
+// no-op unless a tool such as Nsight Systems is attached), so that timelines show the stages by name.
 extern std::atomic<int> g_profile_on;
+extern const char* const kStageNames[];
 int prof_begin(int stage, cudaStream_t st);
 void prof_end(int idx, cudaStream_t st);
 struct StageScope {
   int idx = -1;
   cudaStream_t st;
   StageScope(int stage, cudaStream_t s) : st(s) {
+    nvtxRangePushA(kStageNames[stage]);
     if (g_profile_on.load(std::memory_order_relaxed)) idx = prof_begin(stage, s);
   }
   ~StageScope() {
     if (idx >= 0) prof_end(idx, st);
+    nvtxRangePop();
   }
   StageScope(const StageScope&) = delete;
   StageScope& operator=(const StageScope&) = delete;

@@ -10,10 +10,12 @@ namespace mb200 {
 std::atomic<int> g_profile_on{0};
 namespace {
 struct ProfRegion {
+  int id;
   int stage;
   cudaEvent_t a, b;
   bool closed;
 };
+int g_prof_next_id = 0;
 std::mutex g_prof_mu;
 std::vector<ProfRegion> g_prof_open;       // recorded, not yet folded into the totals
 std::vector<cudaEvent_t> g_prof_free;      // recycled events
@@ -31,9 +33,13 @@ cudaEvent_t prof_event() {
   cudaEventCreate(&e);
   return e;
 }
-void prof_fold() {  // g_prof_mu held
+void prof_fold() {  // g_prof_mu held. Regions still open (begin recorded, end not yet) stay in the list.
+  std::vector<ProfRegion> still_open;
   for (ProfRegion& r : g_prof_open) {
-    if (!r.closed) continue;
+    if (!r.closed) {
+      still_open.push_back(r);
+      continue;
+    }
     float ms = 0.f;
     if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
       g_prof_ms[r.stage] += ms;
@@ -42,7 +48,7 @@ void prof_fold() {  // g_prof_mu held
     g_prof_free.push_back(r.a);
     g_prof_free.push_back(r.b);
   }
-  g_prof_open.clear();
+  g_prof_open.swap(still_open);
 }
 }  // namespace
 
@@ -54,18 +60,30 @@ int prof_begin(int stage, cudaStream_t st) {
   const long long call = g_prof_calls[stage]++;
   const bool per_launch = stage == MB200_STAGE_LCP_BODY || stage == MB200_STAGE_LCP_RATE || stage == MB200_STAGE_LCP_COMM;
   if (per_launch && stride > 1 && call % stride != 0) return -1;
-  ProfRegion r{stage, prof_event(), prof_event(), false};
+  ProfRegion r{g_prof_next_id, stage, prof_event(), prof_event(), false};
   if (!r.a || !r.b) return -1;
+  g_prof_next_id = (g_prof_next_id + 1) & 0x3fffffff;
   cudaEventRecord(r.a, st);
   g_prof_open.push_back(r);
-  return static_cast<int>(g_prof_open.size()) - 1;
+  return r.id;
 }
-void prof_end(int idx, cudaStream_t st) {
+void prof_end(int id, cudaStream_t st) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
-  if (idx < 0 || idx >= static_cast<int>(g_prof_open.size())) return;
-  cudaEventRecord(g_prof_open[idx].b, st);
-  g_prof_open[idx].closed = true;
+  for (size_t k = g_prof_open.size(); k-- > 0;) {  // the region just opened is at or near the back
+    ProfRegion& r = g_prof_open[k];
+    if (r.id == id && !r.closed) {
+      cudaEventRecord(r.b, st);
+      r.closed = true;
+      return;
+    }
+  }
 }
+
+// NVTX range names of the stages (the reference brackets its phases with named regions,
+// alens/tests/performance_tests/NgpHP1.cpp:1503,1643)
+const char* const kStageNames[MB200_STAGE_COUNT] = {"mb200:trigger",   "mb200:broadphase", "mb200:pack",     "mb200:narrow",
+                                                    "mb200:lcp_setup", "mb200:lcp_body",   "mb200:lcp_rate", "mb200:euler",
+                                                    "mb200:lcp_comm",  "mb200:state_comm"};
 
 static thread_local std::string t_error;
 std::atomic<long long> g_launches{0};

@@ -18,16 +18,23 @@ int narrow_phase_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, 
 struct Incidence {
   Scratch<int64_t> ptr;    // n + 1
   Scratch<uint32_t> list;  // 2 * npairs
+  Scratch<int32_t> bad;    // 1: some pair named a body outside [0, n)
 };
 int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, Incidence* inc);
+int check_incidence(cudaStream_t st, const Incidence& inc);  // synchronises; error if `bad` was raised
 
 // The BBPGD solve on contact records (layout: lcp_solve.cu header). rec is modified when U_ext != NULL (phi0 correction).
 // F,T,U,W are written in the order of the bodies the records index; U/W hold the collision velocity only.
+// Form of the lever arms: none (3-DOF, spheres), axial (arm = sigma * half-axis vector of the body: the step's
+// spherocylinders, whose contact points lie on the centre line), general (caller-supplied arm vectors).
+enum { ARM_NONE = 0, ARM_AXIAL = 1, ARM_GENERAL = 2 };
 struct RecordSystem {
   int64_t n, npairs;
-  bool six;
-  const int2* pairs;  // [npairs]
-  D4* rec;            // [npairs] (3-DOF) or [3 npairs] (6-DOF)
+  int arm;
+  const int2* pairs;   // [npairs]
+  D4* rec;             // R0 [npairs]; ARM_GENERAL: + R1, R2 ([3 npairs])
+  const double2* sig;  // ARM_AXIAL: [npairs] {sigma_i, sigma_j}
+  const D4* half;      // ARM_AXIAL: [n] {h, kind}, h = (L/2) (q (x) z_hat)
   const double* quat;
   const double* radius;
   const int32_t* kind;
@@ -59,10 +66,12 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
                     const double* U_ext, const double* W_ext, const double* gamma0, double* gamma_out,
                     double* phi0_out, double* F, double* T, double* U, double* W, mb200_collision_result* result_h,
                     const DistSolve* dist);
+int rate_grid_for(int64_t npairs, int arm);
 // Narrow phase straight into contact records (the step's path).
 // perm (Morton -> caller index, nullable): pairs are evaluated with the lower caller index first.
+// Rods (b1 != NULL): rec = R0 and sig = the axial arm parameters; spheres: rec = R0 only.
 int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const uint32_t* perm, const D4* b0,
-                            const D4* b1, bool six, D4* rec, const Periodic& P);
+                            const D4* b1, D4* rec, double2* sig, const Periodic& P);
 // step.cu: the step after the link list is known (dist != NULL on the multi-GPU path)
 
 

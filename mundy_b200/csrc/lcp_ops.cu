@@ -6,13 +6,19 @@
 namespace mb200 {
 namespace {
 
-__global__ void __launch_bounds__(256) incidence_keys_kernel(int64_t m, const int32_t* __restrict__ pairs_flat,
+// A body index outside [0, n) (caller-supplied pair lists reach this through mb200_resolve_collisions / mb200_apply_*)
+// raises *bad and is counted on body 0, so that nothing is written out of bounds; the entry point then fails.
+__global__ void __launch_bounds__(256) incidence_keys_kernel(int64_t m, int64_t n, const int32_t* __restrict__ pairs_flat,
                                                              uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
-                                                             uint32_t* __restrict__ counts) {
+                                                             uint32_t* __restrict__ counts, int32_t* __restrict__ bad) {
   const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (k >= m) return;
-  const uint32_t b = static_cast<uint32_t>(pairs_flat[k]);
-  keys[k] = b;
+  int64_t b = pairs_flat[k];
+  if (b < 0 || b >= n) {
+    *bad = 1;
+    b = 0;
+  }
+  keys[k] = static_cast<uint32_t>(b);
   vals[k] = static_cast<uint32_t>(k);  // 2 * contact + side
   atomicAdd(counts + b, 1u);
 }
@@ -104,18 +110,30 @@ int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* p
   MB200_TRY(inc->list.alloc(m > 0 ? m : 1, st));
   Scratch<uint32_t> counts, keys, keys_alt, vals_alt;
   MB200_TRY(counts.alloc(n > 0 ? n : 1, st));
+  MB200_TRY(inc->bad.alloc(1, st));
   MB200_CUDA(cudaMemsetAsync(counts.p, 0, (n > 0 ? n : 1) * sizeof(uint32_t), st));
+  MB200_CUDA(cudaMemsetAsync(inc->bad.p, 0, sizeof(int32_t), st));
   if (m > 0) {
+    MB200_REQUIRE(n > 0, "pairs given for an empty body set");
     MB200_TRY(keys.alloc(m, st));
     MB200_TRY(keys_alt.alloc(m, st));
     MB200_TRY(vals_alt.alloc(m, st));
-    incidence_keys_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, pairs, keys.p, inc->list.p, counts.p);
+    incidence_keys_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, n, pairs, keys.p, inc->list.p, counts.p, inc->bad.p);
     MB200_LAUNCHED();
     int bits = 1;
     while ((int64_t(1) << bits) < n) ++bits;
     MB200_TRY(radix_sort_u32(st, m, keys.p, keys_alt.p, inc->list.p, vals_alt.p, bits));
   }
   MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, inc->ptr.p));
+  return MB200_OK;
+}
+
+// For the entry points that take the caller's pair list: synchronises and fails if an index was out of range.
+int check_incidence(cudaStream_t st, const Incidence& inc) {
+  int32_t bad = 0;
+  MB200_CUDA(cudaMemcpyAsync(&bad, inc.bad.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  MB200_CUDA(cudaStreamSynchronize(st));
+  MB200_REQUIRE(bad == 0, "a pair names a body index outside [0, n)");
   return MB200_OK;
 }
 
@@ -173,6 +191,7 @@ int mb200_apply_D(mb200_stream stream, const mb200_contact_op* op, const double*
   cudaStream_t st = as_stream(stream);
   Incidence inc;
   MB200_TRY(build_incidence(st, op->n, op->npairs, op->pairs, &inc));
+  MB200_TRY(check_incidence(st, inc));
   if (six)
     apply_D_kernel<true><<<grid_for(op->n, 128), 128, 0, st>>>(op->n, inc.ptr.p, inc.list.p, gamma, op->normal,
                                                               op->arm_i, op->arm_j, F, T);

@@ -19,7 +19,8 @@ struct mb200_neighbor_links {
   mb200::Incidence inc;              // body-major incidence lists of `pairs`
   // per-step arrays in Morton order (allocated by the step)
   mb200::DevBuf<mb200::D4> b0, b1;
-  mb200::DevBuf<mb200::D4> rec;  // contact records of the current step (lcp_solve.cu)
+  mb200::DevBuf<mb200::D4> rec;  // contact records {n, phi0} of the current step (lcp_solve.cu)
+  mb200::DevBuf<double2> sig;    // rods: axial arm parameters {sigma_i, sigma_j} of the current step
   mb200::DevBuf<double> radius_s, quat_s, vec_a, vec_b, vec_c, vec_d, vec_e, vec_f;
   mb200::DevBuf<int32_t> kind_s;
   mb200::DevBuf<int32_t> flag;  // device flag for the rebuild trigger

@@ -501,6 +501,7 @@ int mb200_resolve_collisions_mobility(mb200_stream stream, const mb200_contact_o
 
   Incidence inc;
   MB200_TRY(build_incidence(st, n, m, op->pairs, &inc));
+  MB200_TRY(check_incidence(st, inc));
   const int blocks = grid_for(m, kRedThreads, kSMs * 4);
   Scratch<double> gam_b, gd_a, gd_b, partials, red;
   MB200_TRY(gam_b.alloc(m, st));

@@ -81,12 +81,13 @@ __global__ void __launch_bounds__(kTile)
   }
 }
 
-// Same arithmetic, written as solver contact records (lcp_solve.cu): R0 = {n, phi0}, R1 = {arm_i, (i,j)}, R2 = {arm_j, 0},
-// one array per record kind: rec[k * npairs + c].
-template <bool RODS, bool SIX>
+// Same arithmetic, written as the solver's contact arrays (lcp_solve.cu): R0 = {n, phi0} and, for rods, the axial arm
+// parameters {sigma_i, sigma_j}.
+template <bool RODS>
 __global__ void __launch_bounds__(256)
     narrow_phase_rec_kernel(int64_t npairs, const int2* __restrict__ pairs, const uint32_t* __restrict__ perm,
-                            const D4* __restrict__ b0, const D4* __restrict__ b1, D4* __restrict__ rec, Periodic P) {
+                            const D4* __restrict__ b0, const D4* __restrict__ b1, D4* __restrict__ rec,
+                            double2* __restrict__ sig, Periodic P) {
   const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (c >= npairs) return;
   const int2 p = __ldg(pairs + c);
@@ -105,32 +106,26 @@ __global__ void __launch_bounds__(256)
     const PairGeom r = pair_geometry<RODS>(b0j, b1j, P.any ? unwrap_to(P, b0j, b0i) : b0i, b1i);
     g.sep = r.sep;
     g.n = V3{-r.n.x, -r.n.y, -r.n.z};
-    g.arm_i = r.arm_j;
-    g.arm_j = r.arm_i;
+    g.sig_i = r.sig_j;
+    g.sig_j = r.sig_i;
   }
-  if (SIX) {
-    const long long bits = (static_cast<long long>(p.y) << 32) | static_cast<long long>(static_cast<uint32_t>(p.x));
-    st256(rec + c, D4{g.n.x, g.n.y, g.n.z, g.sep});
-    st256(rec + npairs + c, D4{g.arm_i.x, g.arm_i.y, g.arm_i.z, __longlong_as_double(bits)});
-    st256(rec + 2 * npairs + c, D4{g.arm_j.x, g.arm_j.y, g.arm_j.z, 0.0});
-  } else {
-    st256(rec + c, D4{g.n.x, g.n.y, g.n.z, g.sep});
-  }
+  st256(rec + c, D4{g.n.x, g.n.y, g.n.z, g.sep});
+  if (RODS) sig[c] = make_double2(g.sig_i, g.sig_j);
 }
 
 }  // namespace
 
 int narrow_phase_to_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, const uint32_t* perm, const D4* b0,
-                            const D4* b1, bool six, D4* rec, const Periodic& P) {
+                            const D4* b1, D4* rec, double2* sig, const Periodic& P) {
   if (npairs == 0) return MB200_OK;
   const int grid = grid_for(npairs, 256);
   const int2* p2 = reinterpret_cast<const int2*>(pairs);
-  if (b1 && six)
-    narrow_phase_rec_kernel<true, true><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, b1, rec, P);
-  else if (!b1 && !six)
-    narrow_phase_rec_kernel<false, false><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, nullptr, rec, P);
+  if (b1 && sig)
+    narrow_phase_rec_kernel<true><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, b1, rec, sig, P);
+  else if (!b1)
+    narrow_phase_rec_kernel<false><<<grid, 256, 0, st>>>(npairs, p2, perm, b0, nullptr, rec, nullptr, P);
   else {
-    set_error("narrow_phase_to_records: rods and 6-DOF records go together");
+    set_error("narrow_phase_to_records: rods need the axial arm array");
     return MB200_ERR_INVALID_ARGUMENT;
   }
   MB200_LAUNCHED();

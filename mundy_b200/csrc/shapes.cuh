@@ -16,6 +16,10 @@ struct PairGeom {
   V3 n;        // unit normal from i to j
   V3 arm_i;    // centre-line closest point minus centre (zero for spheres)
   V3 arm_j;
+  // axial form of the arms: arm = sigma h, h = the body's half-axis vector, sigma = 2 clamp(s, 0, 1) - 1 with s the
+  // segment parameter of the closest point (geom::distance returns the point-segment parameter unclamped,
+  // PointLineSegment.hpp:156-167); 0 for spheres. Equal to the vectors above up to rounding.
+  double sig_i, sig_j;
 };
 
 // Narrow-phase arithmetic for one pair. RODS=false: both bodies are spheres and b1* are not read.
@@ -24,6 +28,7 @@ __device__ inline PairGeom pair_geometry(const D4& b0i, const D4& b1i, const D4&
   PairGeom g;
   g.arm_i = V3{0.0, 0.0, 0.0};
   g.arm_j = V3{0.0, 0.0, 0.0};
+  g.sig_i = 0.0, g.sig_j = 0.0;
   const V3 ci{b0i.x, b0i.y, b0i.z}, cj{b0j.x, b0j.y, b0j.z};
   const double ri = b0i.w, rj = b0j.w;
   const bool rod_i = RODS && (b1i.w != 0.0), rod_j = RODS && (b1j.w != 0.0);
@@ -37,7 +42,7 @@ __device__ inline PairGeom pair_geometry(const D4& b0i, const D4& b1i, const D4&
     return g;
   }
   V3 cp1, cp2, sv;
-  double d, s, t;
+  double d, s = 0.5, t = 0.5;
   if (rod_i && rod_j) {
     const V3 hi{b1i.x, b1i.y, b1i.z}, hj{b1j.x, b1j.y, b1j.z};
     d = dist_segseg(ci - hi, ci + hi, cj - hj, cj + hj, cp1, cp2, s, t, sv);
@@ -54,8 +59,8 @@ __device__ inline PairGeom pair_geometry(const D4& b0i, const D4& b1i, const D4&
   g.sep = d - (ri + rj);
   const double inv = 1.0 / d;
   g.n = sv * inv;
-  if (rod_i) g.arm_i = cp1 - ci;
-  if (rod_j) g.arm_j = cp2 - cj;
+  if (rod_i) g.arm_i = cp1 - ci, g.sig_i = 2.0 * fmin(fmax(s, 0.0), 1.0) - 1.0;
+  if (rod_j) g.arm_j = cp2 - cj, g.sig_j = 2.0 * fmin(fmax(t, 0.0), 1.0) - 1.0;
   return g;
 }
 

@@ -212,7 +212,8 @@ int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodi
         Wext_s = h->vec_b.p;
       }
     }
-    MB200_TRY(h->rec.reserve(static_cast<size_t>(rods ? 3 : 1) * C + 1));
+    MB200_TRY(h->rec.reserve(static_cast<size_t>(C) + 1));
+    if (rods) MB200_TRY(h->sig.reserve(static_cast<size_t>(C) + 1));
     if (h->forces_pending) {  // host entry point: the wrench arrives on the side stream (first read just below)
       MB200_CUDA(cudaStreamWaitEvent(st, h->forces_ev, 0));
       h->forces_pending = false;
@@ -228,8 +229,8 @@ int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodi
     }
     {  // narrow phase on the links
       StageScope ps(MB200_STAGE_NARROW, st);
-      MB200_TRY(narrow_phase_to_records(st, C, h->pairs.p, h->perm.p, h->b0.p, rods ? h->b1.p : nullptr, rods, h->rec.p,
-                                        h->periodic));
+      MB200_TRY(narrow_phase_to_records(st, C, h->pairs.p, h->perm.p, h->b0.p, rods ? h->b1.p : nullptr, h->rec.p,
+                                        rods ? h->sig.p : nullptr, h->periodic));
     }
     // LCP
     MB200_TRY(h->vec_c.reserve(3 * n));
@@ -238,8 +239,9 @@ int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodi
       MB200_TRY(h->vec_e.reserve(3 * n));
       MB200_TRY(h->vec_f.reserve(3 * n));
     }
-    RecordSystem sys{n, C, rods, reinterpret_cast<const int2*>(h->pairs.p), h->rec.p, rods ? h->quat_s.p : nullptr,
-                     h->radius_s.p, rods ? h->kind_s.p : nullptr, params->viscosity, params->dt};
+    RecordSystem sys{n, C, rods ? ARM_AXIAL : ARM_NONE, reinterpret_cast<const int2*>(h->pairs.p), h->rec.p,
+                     rods ? h->sig.p : nullptr, rods ? h->b1.p : nullptr, rods ? h->quat_s.p : nullptr, h->radius_s.p,
+                     rods ? h->kind_s.p : nullptr, params->viscosity, params->dt};
     mb200_lcp_params lp{params->tol, params->max_iters, params->fixed_iters};
     double* F_s = h->vec_c.p;
     double* U_s = h->vec_d.p;

@@ -351,6 +351,28 @@ def resolve_collisions(op, phi0, gamma, tol, max_iters, fixed_iters=-1, U_ext=No
     return res, F, T, U, W
 
 
+ARM_NONE, ARM_AXIAL, ARM_GENERAL = 0, 1, 2
+
+
+def resolve_collisions_axial(op, sigma, length, phi0, gamma, tol, max_iters, fixed_iters=-1, U_ext=None, W_ext=None):
+    """Arms in axial form (sigma (npairs, 2), length (n,)); phi0 and gamma are updated in place. Returns (result, F, T, U, W)."""
+    dev = phi0.device
+    F, U, T, W = (torch.empty((op.n, 3), dtype=torch.float64, device=dev) for _ in range(4))
+    params = capi.LcpParams(tol, max_iters, fixed_iters)
+    res = capi.CollisionResult()
+    check(lib.mb200_resolve_collisions_axial(_stream(), C.byref(op), _f64(sigma), _f64(length), C.byref(params),
+                                             _f64(U_ext), _f64(W_ext), _f64(phi0), _f64(gamma), _f64(F), _f64(T),
+                                             _f64(U), _f64(W), C.byref(res)), "resolve_collisions_axial")
+    return res, F, T, U, W
+
+
+def lcp_reduction_shape(npairs, arm_mode):
+    """(grid, threads) of the solver's deterministic global reductions for npairs contacts (see the header)."""
+    g, t = C.c_int32(), C.c_int32()
+    check(lib.mb200_lcp_reduction_shape(int(npairs), int(arm_mode), C.byref(g), C.byref(t)), "lcp_reduction_shape")
+    return g.value, t.value
+
+
 # G. non-local mobility operators (SURVEY 8f rank 3) ---------------------------------------------------------------
 KERNEL_STOKES, KERNEL_RPY, KERNEL_RPYC, KERNEL_RPY_EXACT = 0, 1, 2, 3
 MOBILITY_LOCAL_DRAG, MOBILITY_NEIGHBORS, MOBILITY_ALL = 0, 1, 2

@@ -248,15 +248,17 @@ def moved_too_much_shapes(pos, quat, length, kind, pos_at_build, quat_at_build, 
                       restype=C.c_int))
 
 
-def narrow_phase(pairs, pos, r, quat=None, length=None, kind=None, arms=False, cell=None):
+def narrow_phase(pairs, pos, r, quat=None, length=None, kind=None, arms=False, cell=None, sigma=False):
+    """sigma=True additionally returns the axial form of the arms, (m, 2): arm_side = sigma_side * half-axis of the body."""
     pairs = _a(pairs, _i)
     m = len(pairs)
     phi, normal = np.empty(m), np.empty((m, 3))
     ai = np.empty((m, 3)) if arms else None
     aj = np.empty((m, 3)) if arms else None
-    _call(orc, "orc_narrow_phase_periodic", m, pairs, _a(pos), _a(quat), _a(r), _a(length), _a(kind, _i), _cell(cell),
-          phi, normal, ai, aj)
-    return phi, normal, ai, aj
+    sg = np.zeros((m, 2)) if sigma else None
+    _call(orc, "orc_narrow_phase_full", m, pairs, _a(pos), _a(quat), _a(r), _a(length), _a(kind, _i), _cell(cell),
+          phi, normal, ai, aj, sg)
+    return (phi, normal, ai, aj, sg) if sigma else (phi, normal, ai, aj)
 
 
 def apply_D(n, pairs, normal, gamma, arm_i=None, arm_j=None):
@@ -290,17 +292,26 @@ def apply_A(n, pairs, normal, r, mu, dt, x, arm_i=None, arm_j=None, quat=None, k
 
 
 def resolve_collisions(n, pairs, normal, r, mu, dt, tol, max_it, phi0, gamma0=None, fixed_iters=-1, arm_i=None,
-                       arm_j=None, quat=None, kind=None, U_ext=None, W_ext=None):
-    """Returns dict(res, it, max_disp, gamma, phi0, F, T, U, W). Inputs are not modified."""
+                       arm_j=None, quat=None, kind=None, U_ext=None, W_ext=None, sigma=None, length=None):
+    """Returns dict(res, it, max_disp, gamma, phi0, F, T, U, W). Inputs are not modified.
+    sigma (m, 2) + length: arms in axial form (what the device's step runs for spherocylinders) instead of arm_i/arm_j."""
     pairs = _a(pairs, _i)
     m = len(pairs)
     phi0 = _a(phi0).copy()
     gamma = np.zeros(m) if gamma0 is None else _a(gamma0).copy()
-    six = arm_i is not None
+    six = arm_i is not None or sigma is not None
     F, U = np.zeros((n, 3)), np.zeros((n, 3))
     T = np.zeros((n, 3)) if six else None
     W = np.zeros((n, 3)) if six else None
     res = CollisionResult()
+    if sigma is not None:
+        fn = orc.orc_resolve_collisions_axial
+        fn.restype = None
+        fn(C.c_long(n), C.c_long(m), _p(pairs), _p(_a(normal)), _p(_a(sigma)), _p(_a(quat)), _p(_a(length)), _p(_a(r)),
+           _p(_a(kind, _i)), C.c_double(mu), C.c_double(dt), C.c_double(tol), C.c_int(max_it), C.c_int(fixed_iters),
+           _p(_a(U_ext)), _p(_a(W_ext)), _p(phi0), _p(gamma), _p(F), _p(T), _p(U), _p(W), C.byref(res))
+        return dict(res=res.max_abs_projected_sep, it=res.ite_count, max_disp=res.max_displacement, gamma=gamma,
+                    phi0=phi0, F=F, T=T, U=U, W=W)
     fn = orc.orc_resolve_collisions
     fn.restype = None
     fn(C.c_long(n), C.c_long(m), _p(pairs), _p(_a(normal)), _p(_a(arm_i)), _p(_a(arm_j)), _p(_a(quat)), _p(_a(r)),
@@ -409,12 +420,13 @@ def collision_step(state, w, links, buffer, filt, mu, dt, tol, max_it, fixed, F_
         links = (pairs, c.copy(), None if q is None else q.copy())
     pairs = links[0]
     arms = kind is not None
-    phi, nrm, ai, aj = narrow_phase(pairs, c, r, q, L, kind, arms, cell)
+    phi, nrm, _, _, sg = narrow_phase(pairs, c, r, q, L, kind, False, cell, sigma=True)
     Uext = Wext = None
     if F_ext is not None:
         Uext, Wext = apply_M(r, mu, F_ext, np.zeros_like(F_ext) if arms else None, q, kind)
-    out = resolve_collisions(len(r), pairs, nrm, r, mu, dt, tol, max_it, phi, fixed_iters=fixed, arm_i=ai,
-                                    arm_j=aj, quat=q, kind=kind, U_ext=Uext, W_ext=Wext)
+    # spherocylinders: arms in axial form, as the device's step
+    out = resolve_collisions(len(r), pairs, nrm, r, mu, dt, tol, max_it, phi, fixed_iters=fixed, quat=q, kind=kind,
+                             U_ext=Uext, W_ext=Wext, sigma=sg if arms else None, length=L)
     U = out["U"] + (Uext if Uext is not None else 0.0)
     Wt = (out["W"] + (Wext if Wext is not None else 0.0)) if arms else None
     c2, q2 = euler_update(c, U, dt, q, kind, Wt)
