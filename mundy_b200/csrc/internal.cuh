@@ -18,6 +18,7 @@ int narrow_phase_records(cudaStream_t st, int64_t npairs, const int32_t* pairs, 
 struct Incidence {
   Scratch<int64_t> ptr;    // n + 1
   Scratch<uint32_t> list;  // 2 * npairs
+  Scratch<uint32_t> epos;  // 2 * npairs: epos[2 * contact + side] = position of that entry in `list` (the inverse of it)
   Scratch<int32_t> bad;    // 1: some pair named a body outside [0, n)
 };
 int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, Incidence* inc);

@@ -36,6 +36,11 @@ __global__ void __launch_bounds__(256) coo_keys_kernel(int64_t m, int64_t n, con
   vals[k] = static_cast<uint32_t>(k);  // 2 * link + slot
   if (!empty) atomicAdd(counts + b, 1u);
 }
+__global__ void __launch_bounds__(256) invert_list_kernel(int64_t m, const uint32_t* __restrict__ list,
+                                                          uint32_t* __restrict__ epos) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k < m) epos[list[k]] = static_cast<uint32_t>(k);
+}
 __global__ void __launch_bounds__(256) crs_split_kernel(int64_t m, const uint32_t* __restrict__ vals,
                                                         int32_t* __restrict__ links, int32_t* __restrict__ slots) {
   const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -123,6 +128,9 @@ int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* p
     int bits = 1;
     while ((int64_t(1) << bits) < n) ++bits;
     MB200_TRY(radix_sort_u32(st, m, keys.p, keys_alt.p, inc->list.p, vals_alt.p, bits));
+    MB200_TRY(inc->epos.alloc(m, st));
+    invert_list_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, inc->list.p, inc->epos.p);
+    MB200_LAUNCHED();
   }
   MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, inc->ptr.p));
   return MB200_OK;

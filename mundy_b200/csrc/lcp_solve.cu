@@ -12,12 +12,16 @@
 //                                            copies, K13)
 //   active   = one bit per contact: gamma > 0 or phi0 + dt g < 0, i.e. the contact CAN carry an impulse in the next
 //              iteration whatever the (non-negative) step length; written by the rate pass with one ballot per warp
+//   bmask    = the same bits per BODY: 128 bits each, bit k = the k-th entry of the body's incidence list, so that a body
+//              reads the activity of its contacts with one 16-byte load that depends on nothing; the rate pass flips the
+//              two entry bits of a contact (atomicXor) only when its activity changes. Entries beyond the 128th of a body
+//              (dense packings without a search filter) are always evaluated.
 //   body: mob[b] = {axis, +r (rod) | -r (sphere)}, half[b] = {h, kind}; velocity records {U, 0} (+ {V, 0}; V = omega x h
 //         for ARM_AXIAL, omega for ARM_GENERAL): 64 MB at 10^6 rods, gathered by the rate pass out of L2
 //
 // One iteration = two kernels, no host round trip (the reference blocks the host twice per iteration):
-//   body_pass : a thread per body walks the body's incidence list in ascending (contact, side) order. Contacts whose
-//               `active` bit is clear have gamma = 0 in this iteration and are skipped without touching their data
+//   body_pass : a thread per body visits the set bits of its `bmask` words in ascending (contact, side) order:
+//               contacts whose bit is clear have gamma = 0 in this iteration and are neither looked up nor loaded
 //               (about four in five at cfg3); for the others gamma = max(gamma_prev - alpha (phi0 + dt g_prev), 0)
 //               (KokkosLCP.cpp:655-664) is re-derived from the state and the wrench summed in registers: F = D gamma
 //               without atomics, bit-identical to a serial loop. U = M F; velocity records written (bodies whose
@@ -26,6 +30,10 @@
 //               products; the last CTA to finish reduces the per-CTA partials in index order and advances alpha / done.
 // Every kernel returns at once when `done` is set, so the host enqueues iterations in batches and reads the 48-byte
 // solver state back between batches only.
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
 #include "comm.cuh"
 #include "internal.cuh"
 #include "lcp.cuh"
@@ -54,8 +62,10 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
   const D4* mob;       // [n] mobility records
   const int64_t* inc_ptr;
   const uint32_t* inc_list;
+  const uint32_t* inc_epos;  // [2 npairs] entry (2 c + side) -> its position in inc_list
   double2* state;    // [npairs]
   uint32_t* active;  // [ceil(npairs / 32)]
+  unsigned long long* bmask;  // [2 n] the active bits per body, in incidence order (first 128 entries of each body)
   uint8_t* vzero;    // [n] 1 = the body's velocity records hold zeros
   D4* vel;           // [n] (3-DOF) or [2n] (6-DOF)
   double mu, dt, tol;
@@ -179,15 +189,30 @@ __global__ void __launch_bounds__(256)
   if (gamma) gamma[c] = state[c].x;
 }
 
+constexpr int kMaskBits = 128;  // incidence entries per body covered by bmask
+// The two entry bits of contact c = (i, j) change with its activity.
+__device__ inline void flip_entries(const uint32_t* __restrict__ epos, const int64_t* __restrict__ ptr,
+                                    unsigned long long* bmask, int64_t c, const int2& p) {
+  const int64_t bi = static_cast<int64_t>(__ldg(epos + 2 * c)) - __ldg(ptr + p.x);
+  const int64_t bj = static_cast<int64_t>(__ldg(epos + 2 * c + 1)) - __ldg(ptr + p.y);
+  if (bi < kMaskBits) atomicXor(bmask + 2 * static_cast<int64_t>(p.x) + (bi >> 6), 1ull << (bi & 63));
+  if (bj < kMaskBits) atomicXor(bmask + 2 * static_cast<int64_t>(p.y) + (bj >> 6), 1ull << (bj & 63));
+}
+
 // Initial state {gamma0, 0}; active bit = gamma0 > 0 (what the initial body pass needs). Whole warps: one ballot each.
+// bmask was zeroed before.
 __global__ void __launch_bounds__(256) init_state_kernel(int64_t npairs, const double* __restrict__ gamma0,
-                                                         double2* __restrict__ state, uint32_t* __restrict__ active) {
+                                                         double2* __restrict__ state, uint32_t* __restrict__ active,
+                                                         const int2* __restrict__ pairs, const uint32_t* __restrict__ epos,
+                                                         const int64_t* __restrict__ ptr, unsigned long long* bmask) {
   const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool valid = c < npairs;
   const double g0 = (valid && gamma0) ? gamma0[c] : 0.0;
   if (valid) state[c] = make_double2(g0, 0.0);
-  const uint32_t bits = __ballot_sync(0xffffffffu, valid && g0 > 0.0);
+  const bool flag = valid && g0 > 0.0;
+  const uint32_t bits = __ballot_sync(0xffffffffu, flag);
   if ((threadIdx.x & 31) == 0 && c - (c & 31) < npairs) active[c >> 5] = bits;
+  if (flag) flip_entries(epos, ptr, bmask, c, pairs[c]);
 }
 
 // gdot of one contact from the gathered velocity records. ARM_AXIAL: vi = Ui + sigma_i Vi, V = omega x h (the body pass
@@ -238,7 +263,13 @@ __global__ void __launch_bounds__(256)
 
 // ---- iteration kernels ---------------------------------------------------------------------------------------------
 constexpr int kBodyThreads = 128;
-constexpr int kChunk = 4;  // incidence entries whose loads are in flight together, per thread
+#ifndef MB200_BODY_CHUNK
+#define MB200_BODY_CHUNK 2
+#endif
+// Incidence entries whose loads are in flight together, per thread. Measured at cfg3 (body pass, us): 1: 66.5, 2: 65.6,
+// 3: 77, 4: 76 (registers 72 / 72 / 96 / 116: occupancy matters more than the second pair of requests, a body has 1.6
+// active contacts on average); requesting the body's own records ahead of the contact records: 69.4 (96 registers).
+constexpr int kChunk = MB200_BODY_CHUNK;
 
 // MODE 0: gamma is read from the state (initial pass and final pass). MODE 1: gamma re-derived from the previous state.
 // FINAL: writes F,T,U,W in the solver's body order and reduces max |U| into state->vmax (single launch at the end).
@@ -262,33 +293,33 @@ __global__ void __launch_bounds__(kBodyThreads)
   const double* sigp = reinterpret_cast<const double*>(a.sig);
   double speed = 0.0;
 
-  for (int64_t b = static_cast<int64_t>(blockIdx.x) * kBodyThreads + t; b < a.n; b += stride) {
+  // Bodies are visited from the last to the first: the rate pass walks the contacts upwards, so the state, normal and
+  // arm records of the highest contacts (the last ~100 MB it touched) are still in the 126 MB L2 when this kernel starts
+  // with the highest bodies, and the velocity records this kernel writes last (the lowest bodies) are there for the
+  // rate pass that follows.
+  for (int64_t bi = static_cast<int64_t>(blockIdx.x) * kBodyThreads + t; bi < a.n; bi += stride) {
+    const int64_t b = a.n - 1 - bi;
     // peer mode: ghost rows belong to their owners, who store into them from their own GPUs
     if (!FINAL && a.owned && __ldg(a.owned + b) == 0) continue;
     const int64_t beg = __ldg(a.inc_ptr + b), end = __ldg(a.inc_ptr + b + 1);
+    unsigned long long m0, m1;  // the body's active bits: one load, independent of the pointers
+    asm("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(m0), "=l"(m1) : "l"(a.bmask + 2 * b));
     double acc[NC];
 #pragma unroll
     for (int k = 0; k < NC; ++k) acc[k] = 0.0;
     bool any = false;
-    for (int64_t k0 = beg; k0 < end; k0 += kChunk) {
+    // kChunk entries at a time: entry words, then the records of all of them, are loaded as groups of independent
+    // requests before their first use; contributions are added in entry order
+    auto add_entries = [&](const int64_t (&pos)[kChunk]) {
       uint32_t e[kChunk];
-      bool on[kChunk];
       double2 sp[kChunk];
       D4 r0[kChunk], ra[kChunk];
       double sg[kChunk];
 #pragma unroll
-      for (int u = 0; u < kChunk; ++u) e[u] = (k0 + u < end) ? __ldg(a.inc_list + k0 + u) : 0xffffffffu;
+      for (int u = 0; u < kChunk; ++u) e[u] = (pos[u] >= 0) ? __ldg(a.inc_list + pos[u]) : 0xffffffffu;
 #pragma unroll
       for (int u = 0; u < kChunk; ++u) {
-        on[u] = e[u] != 0xffffffffu;
-        if (on[u] && use_mask) {
-          const uint32_t c = e[u] >> 1;
-          on[u] = (__ldg(a.active + (c >> 5)) >> (c & 31u)) & 1u;
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < kChunk; ++u) {
-        if (on[u]) {
+        if (e[u] != 0xffffffffu) {
           const int64_t c = e[u] >> 1;
           const int side = e[u] & 1u;
           sp[u] = ldg128(a.state + c);
@@ -299,7 +330,7 @@ __global__ void __launch_bounds__(kBodyThreads)
       }
 #pragma unroll
       for (int u = 0; u < kChunk; ++u) {
-        if (on[u]) {
+        if (e[u] != 0xffffffffu) {
           any = true;
           const bool is_j = e[u] & 1u;
           const double g = gamma_of<MODE>(sp[u], r0[u].w, alpha, a.dt, first);
@@ -317,6 +348,31 @@ __global__ void __launch_bounds__(kBodyThreads)
           }
         }
       }
+    };
+    // Positions of the entries to evaluate, ascending: the set bits of the body's mask words, then the entries past the
+    // mask's reach; every entry when the mask cannot be used.
+    int64_t kover = beg + kMaskBits;
+    if (!use_mask) m0 = 0, m1 = 0, kover = beg;
+    auto next_pos = [&]() -> int64_t {
+      if (m0) {
+        const int64_t p = beg + (__ffsll(static_cast<long long>(m0)) - 1);
+        m0 &= m0 - 1;
+        return p;
+      }
+      if (m1) {
+        const int64_t p = beg + 64 + (__ffsll(static_cast<long long>(m1)) - 1);
+        m1 &= m1 - 1;
+        return p;
+      }
+      return (kover < end) ? kover++ : -1;
+    };
+    for (;;) {
+      int64_t pos[kChunk];
+      pos[0] = next_pos();
+      if (pos[0] < 0) break;
+#pragma unroll
+      for (int u = 1; u < kChunk; ++u) pos[u] = (pos[u - 1] >= 0) ? next_pos() : -1;
+      add_entries(pos);
     }
 
     // epilogue: U = M F; velocity records (and, multi-GPU, their ghost copies on the peers) or the solver's outputs
@@ -402,6 +458,53 @@ __global__ void __launch_bounds__(kBodyThreads)
 }
 
 constexpr int kRateThreads = 256;
+constexpr int kRateStages = 3;  // tiles of kRateThreads contacts in flight per CTA
+
+// ---- bulk asynchronous copies global -> shared (the TMA engine's 1-D form; SASS: UBLKCP) with mbarrier completion ----
+__device__ inline uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ inline void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ inline void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ inline void mbar_arrive(uint64_t* bar) {  // release at CTA scope (the default)
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ inline void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+// size: a multiple of 16 bytes; both addresses 16-byte aligned
+__device__ inline void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// One pipeline stage of the rate pass: the contiguous per-contact arrays of kRateThreads consecutive contacts.
+template <int ARM>
+struct RateStage {
+  static constexpr int kState = 0;
+  static constexpr int kRec0 = kState + kRateThreads * 16;
+  static constexpr int kArm = kRec0 + kRateThreads * 32;  // AXIAL: sigma pairs; GENERAL: R1 then R2
+  static constexpr int kPairs = kArm + (ARM == ARM_AXIAL ? kRateThreads * 16 : (ARM == ARM_GENERAL ? kRateThreads * 64 : 0));
+  static constexpr int kBytes = kPairs + kRateThreads * 8;
+};
+template <int ARM>
+constexpr int rate_smem_bytes() {
+  return kRateStages * RateStage<ARM>::kBytes;
+}
 
 // End of an operator application: residual test, next BB step length, iteration cap (KokkosLCP.cpp:735-750, 785-848).
 __device__ inline void advance_state(LcpState* s, double res, double xx, double xg, double gg, int it, int mode,
@@ -472,14 +575,96 @@ __device__ inline D4 ld_vel(const D4* p) {
 // a.halo_seq; the last CTA stores this rank's four totals into every rank's control block, publishes a.red_seq, waits for
 // the other ranks' totals and reduces them in rank order, so that every rank advances to the same alpha / done without
 // a collective call or a host round trip.
+// One contact of the rate pass: gamma of this iteration, g = D^T U from the gathered velocity records, the new state,
+// the contact's terms of the residual and of the three BB sums. Returns the contact's activity for the next iteration.
 template <int ARM, int MODE, bool PEER>
+__device__ inline bool rate_contact(const LcpArgs& a, int64_t c, const double2& sp, const D4& r0, const D4& r1,
+                                    const D4& r2, const double2& sg, const int2& p, double alpha, int first, double& res,
+                                    double& xx, double& xg, double& gg) {
+  const V3 n{r0.x, r0.y, r0.z};
+  V3 ui, uj, wi{0, 0, 0}, wj{0, 0, 0};
+  const V3 ai{r1.x, r1.y, r1.z}, aj{r2.x, r2.y, r2.z};
+  if (ARM != ARM_NONE) {
+    const D4 v0 = ld_vel<PEER>(a.vel + 2 * p.x), v1 = ld_vel<PEER>(a.vel + 2 * p.x + 1);
+    const D4 v2 = ld_vel<PEER>(a.vel + 2 * p.y), v3 = ld_vel<PEER>(a.vel + 2 * p.y + 1);
+    ui = V3{v0.x, v0.y, v0.z}, wi = V3{v1.x, v1.y, v1.z};
+    uj = V3{v2.x, v2.y, v2.z}, wj = V3{v3.x, v3.y, v3.z};
+  } else {
+    const D4 v0 = ld_vel<PEER>(a.vel + p.x), v2 = ld_vel<PEER>(a.vel + p.y);
+    ui = V3{v0.x, v0.y, v0.z}, uj = V3{v2.x, v2.y, v2.z};
+  }
+  const double gam = gamma_of<MODE>(sp, r0.w, alpha, a.dt, first);
+  const double g = rate_of<ARM>(n, ui, uj, wi, wj, ai, aj, sg.x, sg.y);
+  a.state[c] = make_double2(gam, g);
+  const double sep_new = r0.w + a.dt * g;  // KokkosLCP.cpp:500-521
+  if (!a.counted || a.counted[c]) {  // a cut contact is summed by the rank that owns its first body
+    const double v = (gam < 1e-12) ? fabs(fmin(sep_new, 0.0)) : fabs(sep_new);
+    res = fmax(res, v);
+    if (MODE == 1) {  // KokkosLCP.cpp:536-556
+      const double xd = gam - sp.x;
+      const double gd = a.dt * (g - sp.y);
+      xx += xd * xd;
+      xg += xd * gd;
+      gg += gd * gd;
+    }
+  }
+  // can the contact carry an impulse in the next iteration? (the one after the initial pass takes g = 0, :756)
+  return gam > 0.0 || (MODE == 0 ? r0.w : sep_new) < 0.0;
+}
+
+// The four contiguous per-contact streams (state, {n, phi0}, arm data, pair ids) do not go through the load/store unit:
+// one thread hands whole tiles of kRateThreads contacts to the bulk-copy engine (cp.async.bulk -> shared memory, completion
+// counted on an mbarrier), kRateStages tiles ahead of the tile being worked on, so that the memory-level parallelism of the
+// streams no longer depends on registers or resident warps; the LSU carries only the velocity gathers (out of L2) and the
+// state stores. Tiles go round-robin over the persistent grid (tile = blockIdx.x + k gridDim.x), the same contact order
+// per thread as a grid-stride loop, which is the order the deterministic sums are defined in (mb200_lcp_reduction_shape).
+// The last, partial tile takes plain loads.
+// BULK = false is the same kernel with every tile on plain (coalesced 128/256-bit) loads and no shared-memory staging.
+// Measured at cfg3: the pass is bound by the load/store unit's wavefronts of the VELOCITY GATHERS
+// (about 84 of the 106 wavefronts a warp issues per 32 contacts), which the bulk copies do not relieve, and eight warps
+// released together by one barrier issue their gathers in bursts: 78 us against 66 us. The plain form is the default;
+// MB200_RATE_PIPELINE=bulk selects the staged one.
+template <int ARM, int MODE, bool PEER, bool BULK>
 __global__ void __launch_bounds__(kRateThreads) rate_pass_kernel(LcpArgs a, int it, int first) {
   if (a.state_blk->done) return;
+  using St = RateStage<ARM>;
+  extern __shared__ __align__(128) unsigned char stage_mem[];
+  __shared__ __align__(8) uint64_t full_bar[kRateStages];   // bytes of a tile have landed (bulk copies complete_tx)
+  __shared__ __align__(8) uint64_t empty_bar[kRateStages];  // every thread has taken its contact out of the stage
   __shared__ double sh[33];
   __shared__ bool is_last;
   const double alpha = (MODE == 1) ? a.state_blk->alpha : 0.0;
   double res = -1.0, xx = 0.0, xg = 0.0, gg = 0.0;
   const int t = threadIdx.x;
+  const int64_t G = gridDim.x;
+  const int64_t ntiles = (a.npairs + kRateThreads - 1) / kRateThreads;
+  const int64_t nfull = BULK ? a.npairs / kRateThreads : 0;
+  auto issue = [&](int64_t tile, int s) {  // thread 0: tile -> stage s
+    unsigned char* base = stage_mem + s * St::kBytes;
+    const int64_t c0 = tile * kRateThreads;
+    mbar_expect_tx(&full_bar[s], St::kBytes);
+    bulk_g2s(base + St::kState, a.state + c0, kRateThreads * 16, &full_bar[s]);
+    bulk_g2s(base + St::kRec0, a.rec + c0, kRateThreads * 32, &full_bar[s]);
+    if (ARM == ARM_AXIAL) bulk_g2s(base + St::kArm, a.sig + c0, kRateThreads * 16, &full_bar[s]);
+    if (ARM == ARM_GENERAL) {
+      bulk_g2s(base + St::kArm, a.rec + a.npairs + c0, kRateThreads * 32, &full_bar[s]);
+      bulk_g2s(base + St::kArm + kRateThreads * 32, a.rec + 2 * a.npairs + c0, kRateThreads * 32, &full_bar[s]);
+    }
+    bulk_g2s(base + St::kPairs, a.pairs + c0, kRateThreads * 8, &full_bar[s]);
+  };
+  if (BULK && t == 0) {
+#pragma unroll
+    for (int s = 0; s < kRateStages; ++s) mbar_init(&full_bar[s], 1), mbar_init(&empty_bar[s], kRateThreads);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (BULK) __syncthreads();
+  if (BULK && t == 0) {  // the streams do not depend on the peers' halo: they start before the wait below
+#pragma unroll
+    for (int s = 0; s < kRateStages; ++s) {
+      const int64_t tile = blockIdx.x + s * G;
+      if (tile < nfull) issue(tile, s);
+    }
+  }
   if (PEER) {
     if (t < a.peer->world && t != a.peer->me && !wait_flag(&a.peer->ctrl[a.peer->me]->halo_flag[t], a.halo_seq)) {
       a.state_blk->error = 1;
@@ -487,55 +672,63 @@ __global__ void __launch_bounds__(kRateThreads) rate_pass_kernel(LcpArgs a, int 
     }
     __syncthreads();
   }
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * kRateThreads;
-  // whole warps walk 32 consecutive contacts (the active bits of a warp's contacts are one word)
-  for (int64_t cw = static_cast<int64_t>(blockIdx.x) * kRateThreads + (t & ~31); cw < a.npairs; cw += stride) {
+  for (int64_t k = 0;; ++k) {
+    const int64_t tile = blockIdx.x + k * G;
+    if (tile >= ntiles) break;
+    const int s = static_cast<int>(k % kRateStages);
+    const int64_t cw = tile * kRateThreads + (t & ~31);  // whole warps walk 32 consecutive contacts: one word of bits
     const int64_t c = cw + (t & 31);
     const bool valid = c < a.npairs;
-    bool flag = false;
-    if (valid) {
-      const double2 sp = ld128(a.state + c);
-      const D4 r0 = ldg256(a.rec + c);
-      const int2 p = __ldg(a.pairs + c);
-      const V3 n{r0.x, r0.y, r0.z};
-      V3 ui, uj, wi{0, 0, 0}, wj{0, 0, 0}, ai{0, 0, 0}, aj{0, 0, 0};
-      double si = 0.0, sj = 0.0;
-      if (ARM != ARM_NONE) {
-        const D4 v0 = ld_vel<PEER>(a.vel + 2 * p.x), v1 = ld_vel<PEER>(a.vel + 2 * p.x + 1);
-        const D4 v2 = ld_vel<PEER>(a.vel + 2 * p.y), v3 = ld_vel<PEER>(a.vel + 2 * p.y + 1);
-        ui = V3{v0.x, v0.y, v0.z}, wi = V3{v1.x, v1.y, v1.z};
-        uj = V3{v2.x, v2.y, v2.z}, wj = V3{v3.x, v3.y, v3.z};
-        if (ARM == ARM_AXIAL) {
-          const double2 sg = ldg128(a.sig + c);
-          si = sg.x, sj = sg.y;
-        } else {
-          const D4 r1 = ldg256(a.rec + a.npairs + c), r2 = ldg256(a.rec + 2 * a.npairs + c);
-          ai = V3{r1.x, r1.y, r1.z}, aj = V3{r2.x, r2.y, r2.z};
-        }
-      } else {
-        const D4 v0 = ld_vel<PEER>(a.vel + p.x), v2 = ld_vel<PEER>(a.vel + p.y);
-        ui = V3{v0.x, v0.y, v0.z}, uj = V3{v2.x, v2.y, v2.z};
+    double2 sp = make_double2(0.0, 0.0), sg = make_double2(0.0, 0.0);
+    D4 r0{0.0, 0.0, 0.0, 0.0}, r1{0.0, 0.0, 0.0, 0.0}, r2{0.0, 0.0, 0.0, 0.0};
+    int2 p = make_int2(0, 0);
+    if (BULK && tile < nfull) {
+      mbar_wait(&full_bar[s], static_cast<uint32_t>((k / kRateStages) & 1));
+      const unsigned char* base = stage_mem + s * St::kBytes;
+      sp = reinterpret_cast<const double2*>(base + St::kState)[t];
+      r0 = reinterpret_cast<const D4*>(base + St::kRec0)[t];
+      if (ARM == ARM_AXIAL) sg = reinterpret_cast<const double2*>(base + St::kArm)[t];
+      if (ARM == ARM_GENERAL) {
+        r1 = reinterpret_cast<const D4*>(base + St::kArm)[t];
+        r2 = reinterpret_cast<const D4*>(base + St::kArm + kRateThreads * 32)[t];
       }
-      const double gam = gamma_of<MODE>(sp, r0.w, alpha, a.dt, first);
-      const double g = rate_of<ARM>(n, ui, uj, wi, wj, ai, aj, si, sj);
-      a.state[c] = make_double2(gam, g);
-      const double sep_new = r0.w + a.dt * g;  // KokkosLCP.cpp:500-521
-      // can the contact carry an impulse in the next iteration? (the one after the initial pass takes g = 0, :756)
-      flag = gam > 0.0 || (MODE == 0 ? r0.w : sep_new) < 0.0;
-      if (!a.counted || a.counted[c]) {  // a cut contact is summed by the rank that owns its first body
-        const double v = (gam < 1e-12) ? fabs(fmin(sep_new, 0.0)) : fabs(sep_new);
-        res = fmax(res, v);
-        if (MODE == 1) {  // KokkosLCP.cpp:536-556
-          const double xd = gam - sp.x;
-          const double gd = a.dt * (g - sp.y);
-          xx += xd * xd;
-          xg += xd * gd;
-          gg += gd * gd;
+      p = reinterpret_cast<const int2*>(base + St::kPairs)[t];
+      // Hand the stage back as soon as the values have ARRIVED in registers. The stage is refilled by the bulk-copy
+      // engine (the async proxy), which does not queue behind this CTA's shared-memory loads: those share the load/store
+      // unit's queue with the velocity gathers and can sit in it for longer than a refill takes, and neither a barrier
+      // nor a release-arrive waits for their data (observed: whole warps of tile k computing with the records of tile
+      // k + kRateStages). So every loaded word is folded into one value that a (never taken) branch tests: the test
+      // cannot issue before the loads have returned, and the arrive is ordered after it.
+      {
+        long long fold = __double_as_longlong(sp.x) ^ __double_as_longlong(sp.y) ^ __double_as_longlong(r0.x) ^
+                         __double_as_longlong(r0.y) ^ __double_as_longlong(r0.z) ^ __double_as_longlong(r0.w) ^
+                         (static_cast<long long>(p.x) << 32 | static_cast<unsigned>(p.y));
+        if (ARM == ARM_AXIAL) fold ^= __double_as_longlong(sg.x) ^ __double_as_longlong(sg.y);
+        if (ARM == ARM_GENERAL)
+          fold ^= __double_as_longlong(r1.x) ^ __double_as_longlong(r1.y) ^ __double_as_longlong(r1.z) ^
+                  __double_as_longlong(r2.x) ^ __double_as_longlong(r2.y) ^ __double_as_longlong(r2.z);
+        if (fold == 0x7ff8badc0ffee123ll) asm volatile("nanosleep.u32 1;" ::: "memory");
+      }
+      mbar_arrive(&empty_bar[s]);
+      if (t == 0) {
+        const int64_t next = tile + kRateStages * G;
+        if (next < nfull) {
+          mbar_wait(&empty_bar[s], static_cast<uint32_t>((k / kRateStages) & 1));
+          issue(next, s);
         }
       }
+    } else if (valid) {
+      sp = ld128(a.state + c);
+      r0 = ldg256(a.rec + c);
+      p = __ldg(a.pairs + c);
+      if (ARM == ARM_AXIAL) sg = ldg128(a.sig + c);
+      if (ARM == ARM_GENERAL) r1 = ldg256(a.rec + a.npairs + c), r2 = ldg256(a.rec + 2 * a.npairs + c);
     }
+    const uint32_t old_bits = a.active[cw >> 5];  // one address per warp: a broadcast
+    const bool flag = valid && rate_contact<ARM, MODE, PEER>(a, c, sp, r0, r1, r2, sg, p, alpha, first, res, xx, xg, gg);
     const uint32_t bits = __ballot_sync(0xffffffffu, flag);
     if ((t & 31) == 0) a.active[cw >> 5] = bits;
+    if (valid && flag != (((old_bits >> (t & 31)) & 1u) != 0)) flip_entries(a.inc_epos, a.inc_ptr, a.bmask, c, p);
   }
   // per-CTA partials, then the last CTA reduces them in index order (deterministic)
   res = block_max(res, sh, -1.0);
@@ -635,24 +828,67 @@ void launch_body(const LcpArgs& a, int grid, cudaStream_t st, int mode, bool fin
   else
     body_pass_kernel<ARM, 1, false><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
 }
-template <int ARM>
-void launch_rate(const LcpArgs& a, int grid, cudaStream_t st, int mode, int it, int first) {
+bool rate_pipeline_bulk() {
+  static const bool bulk = [] {
+    const char* e = getenv("MB200_RATE_PIPELINE");
+    return e && std::strcmp(e, "bulk") == 0;
+  }();
+  return bulk;
+}
+
+template <int ARM, bool BULK>
+void launch_rate_as(const LcpArgs& a, int grid, cudaStream_t st, int mode, int it, int first) {
+  constexpr int smem = BULK ? rate_smem_bytes<ARM>() : 0;
   if (a.peer) {
     if (mode == 0)
-      rate_pass_kernel<ARM, 0, true><<<grid, kRateThreads, 0, st>>>(a, it, first);
+      rate_pass_kernel<ARM, 0, true, BULK><<<grid, kRateThreads, smem, st>>>(a, it, first);
     else
-      rate_pass_kernel<ARM, 1, true><<<grid, kRateThreads, 0, st>>>(a, it, first);
+      rate_pass_kernel<ARM, 1, true, BULK><<<grid, kRateThreads, smem, st>>>(a, it, first);
   } else {
     if (mode == 0)
-      rate_pass_kernel<ARM, 0, false><<<grid, kRateThreads, 0, st>>>(a, it, first);
+      rate_pass_kernel<ARM, 0, false, BULK><<<grid, kRateThreads, smem, st>>>(a, it, first);
     else
-      rate_pass_kernel<ARM, 1, false><<<grid, kRateThreads, 0, st>>>(a, it, first);
+      rate_pass_kernel<ARM, 1, false, BULK><<<grid, kRateThreads, smem, st>>>(a, it, first);
   }
 }
 template <int ARM>
+void launch_rate(const LcpArgs& a, int grid, cudaStream_t st, int mode, int it, int first) {
+  if (rate_pipeline_bulk())
+    launch_rate_as<ARM, true>(a, grid, st, mode, it, first);
+  else
+    launch_rate_as<ARM, false>(a, grid, st, mode, it, first);
+}
+// Persistent grid of the rate pass: resident CTAs per SM (with the pipeline's shared memory, if any) x 148. Also opts
+// the staged instantiations into their dynamic shared memory size (above the 48 KB default). Per device (the attribute
+// is per context).
+template <int ARM, bool BULK>
+int rate_grid_cap_as() {
+  constexpr int smem = BULK ? rate_smem_bytes<ARM>() : 0;
+  static std::mutex mu;
+  static int cap[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  std::lock_guard<std::mutex> lk(mu);
+  if (cap[dev] == 0) {
+    if (BULK) {
+      cudaFuncSetAttribute(rate_pass_kernel<ARM, 0, false, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      cudaFuncSetAttribute(rate_pass_kernel<ARM, 1, false, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      cudaFuncSetAttribute(rate_pass_kernel<ARM, 0, true, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      cudaFuncSetAttribute(rate_pass_kernel<ARM, 1, true, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    }
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rate_pass_kernel<ARM, 1, true, BULK>, kRateThreads, smem) !=
+            cudaSuccess ||
+        per_sm < 1)
+      per_sm = 1;
+    cap[dev] = per_sm * kSMs;
+  }
+  return cap[dev];
+}
+template <int ARM>
 int rate_grid_cap() {
-  static const int cap = resident_grid(rate_pass_kernel<ARM, 1, false>, kRateThreads);
-  return cap;
+  return rate_pipeline_bulk() ? rate_grid_cap_as<ARM, true>() : rate_grid_cap_as<ARM, false>();
 }
 
 }  // namespace
@@ -699,9 +935,12 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   Scratch<D4> vel, mob;
   Scratch<LcpState> state;
   Scratch<uint32_t> active;
+  Scratch<unsigned long long> bmask;
   Scratch<uint8_t> vzero;
   MB200_TRY(s0.alloc(C > 0 ? C : 1, st));
   MB200_TRY(active.alloc(words, st));
+  MB200_TRY(bmask.alloc(2 * static_cast<size_t>(n > 0 ? n : 1), st));
+  MB200_CUDA(cudaMemsetAsync(bmask.p, 0, 2 * static_cast<size_t>(n > 0 ? n : 1) * sizeof(unsigned long long), st));
   MB200_TRY(vzero.alloc(n > 0 ? n : 1, st));
   MB200_TRY(partials.alloc(4 * static_cast<size_t>(rate_grid), st));
   const bool peer_mode = dist && dist->peer_dev;
@@ -714,8 +953,8 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   LcpArgs a;
   a.n = n, a.npairs = C;
   a.pairs = sys.pairs, a.rec = sys.rec, a.sig = sys.sig, a.half = sys.half, a.mob = mob.p;
-  a.inc_ptr = inc.ptr.p, a.inc_list = inc.list.p;
-  a.state = s0.p, a.active = active.p, a.vzero = vzero.p;
+  a.inc_ptr = inc.ptr.p, a.inc_list = inc.list.p, a.inc_epos = inc.epos.p;
+  a.state = s0.p, a.active = active.p, a.bmask = bmask.p, a.vzero = vzero.p;
   a.vel = peer_mode ? dist->vel_arena : vel.p;
   a.peer = peer_mode ? dist->peer_dev : nullptr;
   a.halo_seq = 0, a.red_seq = 0;
@@ -794,7 +1033,8 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
     StageScope ps(MB200_STAGE_LCP_SETUP, st);
     mobility_records_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, sys.radius, sys.quat, sys.kind, mob.p);
     MB200_LAUNCHED();
-    init_state_kernel<<<grid_for(C > 0 ? C : 1, 256), 256, 0, st>>>(C, gamma0, s0.p, active.p);
+    init_state_kernel<<<grid_for(C > 0 ? C : 1, 256), 256, 0, st>>>(C, gamma0, s0.p, active.p, sys.pairs, inc.epos.p,
+                                                                    inc.ptr.p, bmask.p);
     MB200_LAUNCHED();
     if (U_ext && C > 0) {
       if (arm == ARM_NONE)
