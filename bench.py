@@ -239,8 +239,8 @@ def workload_config(args, n, world, exchange=None):
         how = {"peer": "velocity halo stored into the peers' arenas by the body pass and solver sums reduced inside the "
                        "rate pass over peer memory (NVLink)",
                "nccl": "velocity halo by NCCL send/recv and solver sums by NCCL all-gather, per iteration"}.get(exchange)
-        par = (f"{world} ranks, one box of {world}x{n} bodies, Hilbert-curve blocks"
-               + (f"; {how}; state all-gather per step" if how else ""))
+        par = (f"{world} ranks, one box of {world}x{n} bodies, Hilbert-curve blocks, each rank holds its block + ghosts "
+               "fetched from the neighbouring ranks at every rebuild" + (f"; {how}" if how else ""))
     return {"workload": f"{n} spherocylinders/GPU, aspect ratio 10 (r=0.5, L=9), volume fraction {PHI}, uniform random "
                         "(BASELINE.json configs[2])",
             "bodies_per_gpu": n, "mu": MU, "dt": DT, "tol": TOL, "max_iters": MAX_ITERS, "search_buffer": BUFFER,
@@ -271,15 +271,17 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     comm = None
     if world > 1:
-        # weak scaling: world * n bodies in one box at the same density, ordered along the Hilbert curve; every rank
-        # builds the same replica (same seed) and owns one contiguous block of n bodies (mundy_b200/dist.py)
+        # weak scaling: world * n bodies in one box at the same density, ordered along the Hilbert curve; rank r owns the
+        # r-th block of n bodies and holds ONLY that block (mundy_b200/dist.py): the library fetches the ghosts
         from mundy_b200 import dist as mbd
         w = wl.rods(n * world, phi=PHI, radius=RADIUS, length=LENGTH, seed=3)
         w = mbd.reorder(w, mbd.hilbert_order(w["center"]))
+        lo, hi = mbd.owned_range(n * world, world, rank)
+        w = {k: (v[lo:hi] if isinstance(v, np.ndarray) and v.shape[:1] == (n * world,) else v) for k, v in w.items()}
         comm = mbd.Comm(dev)
     else:
         w = wl.rods(n, phi=PHI, radius=RADIUS, length=LENGTH, seed=3)
-    ntot = len(w["radius"])
+    ntot = n * world
 
     def to_dev(x, dtype=torch.float64):
         return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype, device=dev)
@@ -287,7 +289,7 @@ def run_b200(args):
     c, q = to_dev(w["center"]), to_dev(w["quat"])
     r, L, kind = to_dev(w["radius"]), to_dev(w["length"]), to_dev(w["kind"], torch.int32)
     bodies = ops.make_bodies(c, r, q, L, kind)
-    F = torch.zeros((ntot, 3), dtype=torch.float64, device=dev)
+    F = torch.zeros((n, 3), dtype=torch.float64, device=dev)
     links = ops.NeighborLinks().set_search_buffer(BUFFER)
     if filt:
         links.set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
@@ -356,19 +358,16 @@ def run_b200(args):
     e2e = None
     if not args.no_e2e and comm is not None:
         # every rank keeps its OWNED block in pinned host memory: each step uploads it (centres, quaternions, forcing),
-        # all-gathers the blocks into the device replicas, runs the distributed step and reads the owned block back
-        o0 = rank * n
-        hc, hq, hF = (x[o0:o0 + n].cpu().pin_memory() for x in (c, q, F))
-        dc, dq, dF = (torch.empty_like(x[o0:o0 + n]) for x in (c, q, F))
+        # runs the distributed step and reads the advanced block back
+        hc, hq, hF = (x.cpu().pin_memory() for x in (c, q, F))
         e2e_steps = max(3, min(args.steps, 10))
 
         def host_step():
-            for d_, h_, g_ in ((dc, hc, c), (dq, hq, q), (dF, hF, F)):
+            for d_, h_ in ((c, hc), (q, hq), (F, hF)):
                 d_.copy_(h_, non_blocking=True)
-                dist.all_gather_into_tensor(g_, d_)
             mbd.step_dist(links, comm, bodies, MU, DT, TOL, MAX_ITERS, F_ext=F)
-            hc.copy_(c[o0:o0 + n], non_blocking=True)
-            hq.copy_(q[o0:o0 + n], non_blocking=True)
+            hc.copy_(c, non_blocking=True)
+            hq.copy_(q, non_blocking=True)
             torch.cuda.synchronize()
 
         host_step()
@@ -383,8 +382,8 @@ def run_b200(args):
         ms_e = float(t.item())
         e2e = {"value": ntot * e2e_steps / (ms_e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (3 + 4 + 3) * 8 * ntot,
                "d2h_bytes_per_step": (3 + 4) * 8 * ntot, "steps": e2e_steps, "ms_per_step": ms_e / e2e_steps,
-               "api": "per rank: pinned owned block -> H2D -> all-gather into the replicas -> mb200_collision_step_dist "
-                      "-> D2H of the owned block (bytes summed over ranks)"}
+               "api": "per rank: pinned owned block -> H2D -> mb200_collision_step_dist -> D2H of the owned block "
+                      "(bytes summed over ranks)"}
     elif not args.no_e2e:
         hc, hq = c.cpu().pin_memory(), q.cpu().pin_memory()
         hr, hL, hk = r.cpu().pin_memory(), L.cpu().pin_memory(), kind.cpu().pin_memory()

@@ -459,14 +459,17 @@ int mb200_collision_step_host(mb200_neighbor_links* links, mb200_stream stream, 
  * Multi-GPU (one process per GPU, NCCL over NVLink / NVSwitch). Replaces the MPI usage of the STK drivers on this path
  * (scrap/lcp_spheres/NGPSpheresLCP.cpp:371,450-452 all_reduce of the residual and the BB sums; :256-283 ghosting).
  *
- * Decomposition: the caller orders the global body arrays along a space-filling curve (mundy_b200/dist.py: Hilbert
- * index of the centre) and every rank holds a replica of them; rank r OWNS the contiguous index block
- * [r n/W, (r+1) n/W). A rank works on its owned bodies plus the foreign bodies within search reach (ghosts). A link
- * with one owned end is kept by both owners and its gamma is computed redundantly (bit-identically) on both; it is
- * counted in the global sums by the owner of its lower-index body (scrap/UnitTestMundy.cpp:553-555). Per solver
- * iteration the owners' velocity records go to the ghost rows and the ranks' four scalars to every rank: through peer
- * memory from inside the kernels (default) or with NCCL send/recv + all-gather (see mb200_comm_exchange_mode);
- * per step the advanced owned state is all-gathered into every replica.
+ * Decomposition: every rank OWNS a set of bodies (any number; mundy_b200/dist.py orders a global set along the reference's
+ * Hilbert curve of the centres and hands rank r the r-th contiguous block) and passes ONLY those to the library; nothing is
+ * replicated. At every link rebuild the ranks all-gather their owned bounding boxes (7 doubles each), every rank sends
+ * the owned bodies whose search sphere reaches a peer's box to that peer (nearest periodic image when the links carry a
+ * periodic box), and a rank works on the ranks' blocks in rank order: received ghosts and owned bodies in global id order,
+ * hence the same pair orientation everywhere. A link with one owned end is kept by both owners and its gamma is computed
+ * redundantly (bit-identically) on both; it is counted in the global sums by the owner of its lower-id body
+ * (scrap/UnitTestMundy.cpp:553-555). Between rebuilds the owners refresh the ghosts' centres / quaternions once per step.
+ * Per solver iteration the owners' velocity records go to the ghost rows and the ranks' four scalars to every rank: through
+ * peer memory from inside the kernels (default; the body pass handles the ghosted bodies first so that the halo travels
+ * while the interior is processed) or with NCCL send/recv + all-gather (see mb200_comm_exchange_mode).
  * ------------------------------------------------------------------------------------------------------------- */
 typedef struct mb200_comm mb200_comm;
 #define MB200_COMM_ID_BYTES 128
@@ -484,12 +487,14 @@ int mb200_comm_rank(const mb200_comm* comm);
  * all-gather (fallback; forced with the environment variable MB200_DIST_EXCHANGE=nccl). Valid after the first step. */
 int mb200_comm_exchange_mode(const mb200_comm* comm);
 
-/* One collision timestep on the replicated global body set (device arrays of ALL n bodies on every rank; n must be a
- * multiple of the world size). On return every replica holds the advanced centres / quaternions of all bodies.
- * F_ext / T_ext: replicated [3n] or NULL. F_col / U_out: optional [3n]; only the owned block is written.
- * stats_h: links and launches of THIS rank; lcp fields are global. Collective; synchronises the stream. */
+/* One collision timestep of the bodies distributed over the ranks. owned_bodies: device arrays of the bodies THIS rank owns
+ * (n >= 0, may differ between ranks); on return they hold the advanced centres / quaternions. F_ext / T_ext: per owned body
+ * [3n] or NULL (the same choice on every rank). F_col / U_out: optional [3n], per owned body.
+ * stats_h: links and launches of THIS rank; lcp fields are global. Collective; synchronises the stream.
+ * A rank that returns an error before the first collective of the step leaves its peers waiting: arguments must be valid on
+ * every rank (they are checked before anything is exchanged). */
 int mb200_collision_step_dist(mb200_neighbor_links* links, mb200_comm* comm, mb200_stream stream,
-                              const mb200_bodies* global_bodies, const mb200_step_params* params,
+                              const mb200_bodies* owned_bodies, const mb200_step_params* params,
                               const double* F_ext, const double* T_ext, double* F_col, double* U_out,
                               mb200_step_stats* stats_h);
 /* Bodies (owned + ghosts) and ghosts alone in the last distributed build of this rank. */
@@ -518,7 +523,7 @@ enum mb200_stage {
   MB200_STAGE_LCP_RATE = 6,   /* BBPGD: gamma update, g = D^T U, residual, BB dots   one region per launch */
   MB200_STAGE_EULER = 7,      /* velocity totals, Euler update, scatter to the caller's order            */
   MB200_STAGE_LCP_COMM = 8,   /* multi-GPU: velocity halo (pack, NCCL send/recv, unpack), all-gather of the sums */
-  MB200_STAGE_STATE_COMM = 9, /* multi-GPU: all-gather of the advanced body state, rebuild-flag all-reduce       */
+  MB200_STAGE_STATE_COMM = 9, /* multi-GPU: owned block in / out of the local set, per-step refresh of the ghost state   */
   MB200_STAGE_COUNT = 10
 };
 int mb200_profile_enable(int on);

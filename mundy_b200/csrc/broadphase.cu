@@ -527,14 +527,15 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
 }
 
 // Device flag (h->flag) = 1 when some body moved more than half the buffer since the last build. No host sync.
-int links_moved_flag(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b) {
+int links_moved_flag(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, int64_t ref_offset) {
   MB200_TRY(h->flag.reserve(1));
   MB200_CUDA(cudaMemsetAsync(h->flag.p, 0, sizeof(int32_t), st));
   if (b->n == 0) return MB200_OK;
+  MB200_REQUIRE(ref_offset >= 0 && ref_offset + b->n <= h->n, "bodies outside the set the links were built from");
   const bool shape = h->filter == MB200_FILTER_SHAPE_DISTANCE && h->rods;
-  moved_kernel<<<grid_for(b->n, 256), 256, 0, st>>>(b->n, b->center, h->ref_center.p, b->quat, b->length, b->kind,
-                                                   shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p,
-                                                   h->periodic);
+  moved_kernel<<<grid_for(b->n, 256), 256, 0, st>>>(b->n, b->center, h->ref_center.p + 3 * ref_offset, b->quat, b->length,
+                                                   b->kind, shape ? h->ref_b1.p + ref_offset : nullptr, 0.5 * h->buffer,
+                                                   h->flag.p, h->periodic);
   MB200_LAUNCHED();
   return MB200_OK;
 }

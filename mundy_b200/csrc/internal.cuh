@@ -60,6 +60,8 @@ struct DistSolve {
   const int64_t* push_ptr;             // [n + 1] per body: its entries in push_dst (owned boundary bodies only)
   const uint32_t* push_dst;            // rank << 28 | row of the ghost copy in that rank's arena
   const uint8_t* owned_s;              // [n] ownership flags in the solver's (Morton) body order
+  const uint32_t* boundary;            // [n_boundary] bodies with ghost copies, ascending: the body pass takes them first
+  int64_t n_boundary;
   unsigned long long* halo_seq;        // host counters kept in the communicator (monotone across solves)
   unsigned long long* red_seq;
 };

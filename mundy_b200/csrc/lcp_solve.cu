@@ -86,6 +86,10 @@ struct LcpArgs {  // everything the iteration kernels need; passed by value
   // peer mode: per-body list of the ghost rows (rank << 28 | row in that rank's arena) that mirror an owned body
   const int64_t* push_ptr;
   const uint32_t* push_dst;
+  // peer mode: the bodies that have ghost copies (ascending), handled by the first CTAs of the body pass so that the
+  // velocity halo is on its way while the interior bodies are still being processed
+  const uint32_t* boundary;
+  int64_t n_boundary;
 };
 
 // ---- system-scope signalling between GPUs -----------------------------------------------------------------------
@@ -292,18 +296,34 @@ __global__ void __launch_bounds__(kBodyThreads)
   const int64_t stride = static_cast<int64_t>(gridDim.x) * kBodyThreads;
   const double* sigp = reinterpret_cast<const double*>(a.sig);
   double speed = 0.0;
+  // peer mode: work items [0, nb_pad) are the boundary bodies (padded to whole CTAs), the rest all bodies
+  const bool halo = !FINAL && a.push_ptr != nullptr;
+  const int64_t nb_ctas = halo ? (a.n_boundary + kBodyThreads - 1) / kBodyThreads : 0;
+  const int64_t nb_pad = nb_ctas * kBodyThreads;
 
   // Bodies are visited from the last to the first: the rate pass walks the contacts upwards, so the state, normal and
   // arm records of the highest contacts (the last ~100 MB it touched) are still in the 126 MB L2 when this kernel starts
   // with the highest bodies, and the velocity records this kernel writes last (the lowest bodies) are there for the
   // rate pass that follows.
-  for (int64_t bi = static_cast<int64_t>(blockIdx.x) * kBodyThreads + t; bi < a.n; bi += stride) {
-    const int64_t b = a.n - 1 - bi;
-    // peer mode: ghost rows belong to their owners, who store into them from their own GPUs
-    if (!FINAL && a.owned && __ldg(a.owned + b) == 0) continue;
+  for (int64_t wi = static_cast<int64_t>(blockIdx.x) * kBodyThreads + t; wi < nb_pad + a.n; wi += stride) {
+    int64_t b;
+    if (wi < nb_pad) {
+      if (wi >= a.n_boundary) continue;
+      b = __ldg(a.boundary + wi);
+    } else {
+      b = a.n - 1 - (wi - nb_pad);
+    }
+    // everything the body needs first is requested together (the skip tests below must not serialise the loads)
     const int64_t beg = __ldg(a.inc_ptr + b), end = __ldg(a.inc_ptr + b + 1);
     unsigned long long m0, m1;  // the body's active bits: one load, independent of the pointers
     asm("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(m0), "=l"(m1) : "l"(a.bmask + 2 * b));
+    int64_t pk = 0, pke = 0;
+    uint8_t own = 1;
+    if (halo) pk = __ldg(a.push_ptr + b), pke = __ldg(a.push_ptr + b + 1);
+    if (!FINAL && a.owned) own = __ldg(a.owned + b);
+    if (wi >= nb_pad && pke > pk) continue;  // has ghost copies: done by a boundary CTA
+    // peer mode: ghost rows belong to their owners, who store into them from their own GPUs
+    if (!own) continue;
     double acc[NC];
 #pragma unroll
     for (int k = 0; k < NC; ++k) acc[k] = 0.0;
@@ -407,8 +427,7 @@ __global__ void __launch_bounds__(kBodyThreads)
       } else {
         st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
       }
-      if (a.push_ptr) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
-        const int64_t pk = __ldg(a.push_ptr + b), pke = __ldg(a.push_ptr + b + 1);
+      if (halo) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
         for (int64_t k = pk; k < pke; ++k) {
           const uint32_t d = __ldg(a.push_dst + k);
           D4* dst = a.peer->vel[d >> 28];
@@ -431,22 +450,25 @@ __global__ void __launch_bounds__(kBodyThreads)
       if (SIX && W) st3(W, b, w);
     }
   }
-  if (!FINAL && a.push_ptr) {
-    // every CTA's remote stores are ordered before the flag the last CTA publishes to all ranks (release, system scope);
-    // the consumers are the peers' rate_pass_kernels
+  if (halo && blockIdx.x < nb_ctas) {
+    // the boundary CTAs' remote stores are ordered before the flag the last of them publishes to all ranks (release,
+    // system scope); the consumers are the peers' rate_pass_kernels
     // (bar.sync orders the CTA's stores before thread 0's system-scope fence: the grid-sync pattern, one fence per CTA)
     __syncthreads();
     if (t == 0) {
       __threadfence_system();
       const uint32_t ticket = atomicAdd(&a.state_blk->ticket2, 1u);
-      sh[32] = (ticket == gridDim.x - 1) ? 1.0 : 0.0;
-      if (ticket == gridDim.x - 1) a.state_blk->ticket2 = 0;
+      sh[32] = (ticket == nb_ctas - 1) ? 1.0 : 0.0;
+      if (ticket == nb_ctas - 1) a.state_blk->ticket2 = 0;
     }
     __syncthreads();
     if (sh[32] != 0.0 && t < a.peer->world && t != a.peer->me) {  // one lane per rank: the flags leave in parallel
       __threadfence_system();
       st_relaxed_sys(&a.peer->ctrl[t]->halo_flag[a.peer->me], a.halo_seq);
     }
+  } else if (halo && nb_ctas == 0 && blockIdx.x == 0) {
+    // nothing of this rank is ghosted anywhere: the peers still wait for its flag
+    if (t < a.peer->world && t != a.peer->me) st_relaxed_sys(&a.peer->ctrl[t]->halo_flag[a.peer->me], a.halo_seq);
   }
   if (FINAL) {
     const double m = block_max(speed, sh, 0.0);
@@ -926,7 +948,8 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   }
 
   const int rate_grid = rate_grid_for(C, arm);
-  const int body_grid = grid_for(n, kBodyThreads);
+  const int64_t n_boundary = (dist && dist->peer_dev) ? dist->n_boundary : 0;
+  const int body_grid = grid_for(n + (n_boundary + kBodyThreads - 1) / kBodyThreads * kBodyThreads, kBodyThreads);
   const int cgrid = grid_for(C, 256);
   const size_t words = static_cast<size_t>((C + 31) / 32) + 1;
 
@@ -961,6 +984,8 @@ int resolve_records(cudaStream_t st, const RecordSystem& sys, const Incidence& i
   a.owned = peer_mode ? dist->owned_s : nullptr;
   a.push_ptr = peer_mode ? dist->push_ptr : nullptr;
   a.push_dst = peer_mode ? dist->push_dst : nullptr;
+  a.boundary = peer_mode ? dist->boundary : nullptr;
+  a.n_boundary = n_boundary;
   a.mu = sys.mu, a.dt = sys.dt, a.tol = params->tol;
   a.fixed = fixed ? 1 : 0, a.it_cap = it_cap;
   a.state_blk = state.p, a.partials = partials.p;

@@ -2,6 +2,16 @@
 #pragma once
 #include "internal.cuh"
 
+namespace mb200 {
+// Where the g-th received ghost (receive order: peers in rank order) sits in the local set of a rank: the ranks' blocks
+// are laid out in rank order with the owned block in its place (dist_step.cu).
+struct GhostMap {
+  int npeers;
+  int64_t recv_off[17];   // prefix over peers of the received counts
+  int64_t local_beg[16];  // local index of the first ghost of the q-th peer
+};
+}  // namespace mb200
+
 struct mb200_neighbor_links {
   // builder parameters (GenNeighborLinkers.hpp:401-462)
   double buffer = 0.0;
@@ -42,10 +52,14 @@ struct mb200_neighbor_links {
   struct Dist {
     bool built = false;
     int64_t n_global = 0, n_local = 0, n_own = 0, o_beg = 0;
-    mb200::DevBuf<uint32_t> gidx;      // local -> global body index                  [n_local]
     mb200::DevBuf<uint8_t> owned;      // local body owned by this rank                [n_local]
     mb200::DevBuf<double> center, quat, radius, length, fext, text, fcol, uout;   // local body arrays
     mb200::DevBuf<int32_t> kind;
+    // ghost bodies: what this rank sends to / receives from each peer at a rebuild (body records) and per step (state)
+    int64_t bsend_off[17] = {}, brecv_off[17] = {};
+    mb200::DevBuf<uint32_t> bsend_idx;   // owned indices of the bodies ghosted out, peer-major
+    mb200::DevBuf<double> bsend_rec, brecv_rec;
+    mb200::GhostMap gmap;
     mb200::DevBuf<uint8_t> counted;    // contact counted by this rank                 [npairs]
     mb200::DevBuf<uint32_t> inv_perm;  // local caller index -> Morton index           [n_local]
     mb200::DevBuf<uint32_t> send_idx, recv_idx;
@@ -53,6 +67,8 @@ struct mb200_neighbor_links {
     mb200::DevBuf<uint32_t> remote_row;  // [send list] destination rows in the peers' velocity arenas (peer-memory mode)
     mb200::DevBuf<int64_t> push_ptr;     // [n_local + 1] body -> its ghost copies (Morton order)
     mb200::DevBuf<uint32_t> push_dst;    // rank << 28 | row
+    mb200::DevBuf<uint32_t> boundary;    // Morton indices of the bodies with ghost copies, ascending
+    int64_t n_boundary = 0;
     mb200::DevBuf<mb200::D4> sendbuf, recvbuf;
     mb200::DevBuf<double> red;
     mb200::DevBuf<int32_t> flag_all;
@@ -67,7 +83,9 @@ namespace mb200 {
 // owned != NULL (multi-GPU): per-body ownership flags in the caller's order; links between two non-owned bodies are dropped.
 int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, const double* explicit_S,
                 const uint8_t* owned);
-int links_moved_flag(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b);
+// Device flag (h->flag) = 1 when some body of `b` moved more than half the buffer since the last build; body k of `b` is
+// body ref_offset + k of the set the links were built from. No host sync.
+int links_moved_flag(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b, int64_t ref_offset = 0);
 // step.cu
 int step_core(mb200_neighbor_links* h, cudaStream_t st, const mb200_bodies* bodies, const mb200_step_params* params,
               const double* F_ext, const double* T_ext, double* F_col, double* T_col, double* U_out, double* W_out,

@@ -1,9 +1,9 @@
 """Multi-GPU host side: Hilbert-curve ordering of the bodies, the NCCL communicator, the distributed step wrapper, and a
 numpy statement of the decomposition plan (what the device code in csrc/dist_step.cu builds), used by the CPU tests.
 
-Decomposition (include/mundy_b200.h "Multi-GPU"): bodies are sorted along a 3-D Hilbert curve of their centres once
-(`hilbert_order`); rank r owns the contiguous block [r n/W, (r+1) n/W) of that order; every rank keeps a replica of the
-body arrays. The reference decomposes with stk::balance RCB and never names a curve index (mundy/math/Hilbert.hpp
+Decomposition (include/mundy_b200.h "Multi-GPU"): bodies are sorted along a 3-D Hilbert curve of their centres
+(`hilbert_order`); rank r owns the contiguous block [r n/W, (r+1) n/W) of that order and passes ONLY that block to the
+library, which finds, fetches and refreshes the ghost bodies it needs from the other ranks. The reference decomposes with stk::balance RCB and never names a curve index (mundy/math/Hilbert.hpp
 is a curve *generator*); its Hilbert generator and this index function describe the same family of curves: consecutive
 indices are face-adjacent lattice cells (tests/test_dist_cpu.py).
 """
@@ -218,7 +218,8 @@ class Comm:
 
 def step_dist(links, comm, bodies, viscosity, dt, tol, max_iters, fixed_iters=-1, force_rebuild=False, F_ext=None,
               T_ext=None, F_col=None, U_out=None, throw_on_max_iters=False):
-    """One distributed collision step on the replicated global body set (`bodies` = ops.make_bodies of ALL bodies)."""
+    """One distributed collision step. `bodies` = ops.make_bodies of the bodies THIS RANK OWNS (any number, also zero);
+    F_ext / T_ext / F_col / U_out are per owned body. Collective over the communicator."""
     from .ops import _f64, _stream
     params = capi.StepParams(viscosity, dt, tol, max_iters, fixed_iters, int(throw_on_max_iters), int(force_rebuild))
     stats = capi.StepStats()
