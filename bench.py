@@ -48,6 +48,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--bodies", type=int, default=1_000_000, help="spherocylinders per GPU")
+    ap.add_argument("--workload", default="rods", choices=["rods", "mixed"],
+                    help="rods: BASELINE.json configs[2]/[3] (the metric's workload); mixed: configs[4], a dense packing "
+                         "of half spheres half spherocylinders at volume fraction 0.55, search buffer 0.25, no forcing")
     ap.add_argument("--filter", default="shape", choices=["shape", "none"],
                     help="search filter: shape-distance (default) or every bounding-sphere candidate")
     ap.add_argument("--prep", type=int, default=2, help="untimed steps that relax the random initial overlaps")
@@ -232,6 +235,12 @@ def run_reference(args):
     emit(line)
 
 
+def make_workload(wl, args, n):
+    if args.workload == "mixed":
+        return wl.mixed(n, phi=0.55)
+    return wl.rods(n, phi=PHI, radius=RADIUS, length=LENGTH, seed=3)
+
+
 def workload_config(args, n, world, exchange=None):
     if world == 1:
         par = "1 GPU"
@@ -241,11 +250,15 @@ def workload_config(args, n, world, exchange=None):
                "nccl": "velocity halo by NCCL send/recv and solver sums by NCCL all-gather, per iteration"}.get(exchange)
         par = (f"{world} ranks, one box of {world}x{n} bodies, Hilbert-curve blocks, each rank holds its block + ghosts "
                "fetched from the neighbouring ranks at every rebuild" + (f"; {how}" if how else ""))
-    return {"workload": f"{n} spherocylinders/GPU, aspect ratio 10 (r=0.5, L=9), volume fraction {PHI}, uniform random "
-                        "(BASELINE.json configs[2])",
-            "bodies_per_gpu": n, "mu": MU, "dt": DT, "tol": TOL, "max_iters": MAX_ITERS, "search_buffer": BUFFER,
+    what = (f"{n} spherocylinders/GPU, aspect ratio 10 (r=0.5, L=9), volume fraction {PHI}, uniform random "
+            "(BASELINE.json configs[2])") if args.workload == "rods" else (
+        f"{n} bodies/GPU, half spheres (r=1) half spherocylinders (r=0.5, L=4), volume fraction 0.55, uniform random: dense "
+        "packing relaxed by the solver (BASELINE.json configs[4])")
+    return {"workload": what,
+            "bodies_per_gpu": n, "mu": MU, "dt": DT, "tol": TOL, "max_iters": MAX_ITERS,
+            "search_buffer": BUFFER if args.workload == "rods" else 0.25,
             "search_filter": "shape_distance<=2*buffer" if args.filter == "shape" else "none (all bounding-sphere candidates)",
-            "forcing": "attractive ABC flow", "l2": "inputs larger than L2 (contact arrays >= 250 MB per GPU)",
+            "forcing": "attractive ABC flow" if args.workload == "rods" else "none", "l2": "inputs larger than L2 (contact arrays >= 250 MB per GPU)",
             "parallelism": par}
 
 
@@ -274,14 +287,16 @@ def run_b200(args):
         # weak scaling: world * n bodies in one box at the same density, ordered along the Hilbert curve; rank r owns the
         # r-th block of n bodies and holds ONLY that block (mundy_b200/dist.py): the library fetches the ghosts
         from mundy_b200 import dist as mbd
-        w = wl.rods(n * world, phi=PHI, radius=RADIUS, length=LENGTH, seed=3)
+        w = make_workload(wl, args, n * world)
         w = mbd.reorder(w, mbd.hilbert_order(w["center"]))
         lo, hi = mbd.owned_range(n * world, world, rank)
         w = {k: (v[lo:hi] if isinstance(v, np.ndarray) and v.shape[:1] == (n * world,) else v) for k, v in w.items()}
         comm = mbd.Comm(dev)
     else:
-        w = wl.rods(n, phi=PHI, radius=RADIUS, length=LENGTH, seed=3)
+        w = make_workload(wl, args, n)
     ntot = n * world
+    buffer = BUFFER if args.workload == "rods" else 0.25
+    forcing = args.workload == "rods"
 
     def to_dev(x, dtype=torch.float64):
         return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype, device=dev)
@@ -290,7 +305,7 @@ def run_b200(args):
     r, L, kind = to_dev(w["radius"]), to_dev(w["length"]), to_dev(w["kind"], torch.int32)
     bodies = ops.make_bodies(c, r, q, L, kind)
     F = torch.zeros((n, 3), dtype=torch.float64, device=dev)
-    links = ops.NeighborLinks().set_search_buffer(BUFFER)
+    links = ops.NeighborLinks().set_search_buffer(buffer)
     if filt:
         links.set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
 
@@ -298,7 +313,8 @@ def run_b200(args):
 
     def step():
         F.zero_()
-        ops.abc_flow_force(c, F)
+        if forcing:
+            ops.abc_flow_force(c, F)
         if comm is None:
             st = links.step(bodies, MU, DT, TOL, MAX_ITERS, F_ext=F)
         else:
@@ -388,7 +404,7 @@ def run_b200(args):
         hc, hq = c.cpu().pin_memory(), q.cpu().pin_memory()
         hr, hL, hk = r.cpu().pin_memory(), L.cpu().pin_memory(), kind.cpu().pin_memory()
         hF = F.cpu().pin_memory()  # forcing sampled at the current positions, kept for the e2e steps
-        hlinks = ops.NeighborLinks().set_search_buffer(BUFFER)
+        hlinks = ops.NeighborLinks().set_search_buffer(buffer)
         if filt:
             hlinks.set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
         e2e_steps = max(3, min(args.steps, 10))
@@ -486,6 +502,8 @@ def run_b200(args):
     }
     if args.filter != "shape":
         line["metric"] = METRIC + " (search_filter: none, every bounding-sphere candidate is a constraint)"
+    if args.workload != "rods":
+        line["metric"] = "particle-timesteps/s, dense mixed sphere/spherocylinder packing (BASELINE.json configs[4])"
     if comm is not None:
         nl, ng = mbd.local_counts(links)
         line["dist"] = {"rank0_local_bodies": nl, "rank0_ghost_rows": ng, "owned_per_rank": n,

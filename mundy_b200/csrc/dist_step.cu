@@ -78,6 +78,55 @@ struct PeerList {
   int peer[kMaxRanks];
 };
 
+// An occupancy grid of every rank's owned centres (G^3 cells over the bounding box of all bodies, one bit per cell,
+// all-gathered: at most 256 KB per rank). A rank's bounding box is a poor picture of a space-filling-curve block (a few
+// bodies of the next octant stretch it across a whole neighbour); the grid follows the block's shape. The cell edge is
+// about one search radius (G <= 128): a ghost layer selected through the grid is at most one cell thicker than needed.
+constexpr int kOccMaxG = 128;
+struct OccGrid {
+  double lo[3], inv_cell[3];
+  int G, words;  // cells per axis; 64-bit words per rank (G^3 / 64 rounded up)
+};
+__device__ inline int occ_cell(const OccGrid& og, double x, int d) {
+  const int c = static_cast<int>(floor((x - og.lo[d]) * og.inv_cell[d]));
+  return min(max(c, 0), og.G - 1);
+}
+__global__ void __launch_bounds__(256) occupancy_kernel(int64_t n, OccGrid og, const double* __restrict__ center,
+                                                        unsigned long long* __restrict__ mask) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const V3 c = ld3(center, k);
+  const int cell = (occ_cell(og, c.z, 2) * og.G + occ_cell(og, c.y, 1)) * og.G + occ_cell(og, c.x, 0);
+  const unsigned long long bit = 1ull << (cell & 63);
+  if (!(mask[cell >> 6] & bit)) atomicOr(mask + (cell >> 6), bit);
+}
+// Does rank r own a body in a cell that the cube [c - reach, c + reach] touches? (periodic axes: the images too)
+__device__ inline bool occ_reaches(const OccGrid& og, const unsigned long long* __restrict__ mask, const V3& c,
+                                   double reach, const Periodic& P) {
+  int lo[3], hi[3];
+  const double cc[3] = {c.x, c.y, c.z};
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (P.on[d]) {  // unclamped cell range, wrapped below; a reach of half the period or more covers the axis
+      lo[d] = static_cast<int>(floor((cc[d] - reach - og.lo[d]) * og.inv_cell[d]));
+      hi[d] = static_cast<int>(floor((cc[d] + reach - og.lo[d]) * og.inv_cell[d]));
+      if (hi[d] - lo[d] >= og.G - 1) lo[d] = 0, hi[d] = og.G - 1;
+    } else {
+      lo[d] = occ_cell(og, cc[d] - reach, d);
+      hi[d] = occ_cell(og, cc[d] + reach, d);
+    }
+  }
+  for (int z = lo[2]; z <= hi[2]; ++z)
+    for (int y = lo[1]; y <= hi[1]; ++y)
+      for (int x = lo[0]; x <= hi[0]; ++x) {
+        const int G = og.G;
+        const int xw = ((x % G) + G) % G, yw = ((y % G) + G) % G, zw = ((z % G) + G) % G;
+        const int cell = (zw * G + yw) * G + xw;
+        if ((__ldg(mask + (cell >> 6)) >> (cell & 63)) & 1ull) return true;
+      }
+  return false;
+}
+
 // Distance from coordinate x to the interval [lo, hi] along one axis; periodic axis of length L: nearest image.
 __device__ inline double axis_gap(double x, double lo, double hi, bool periodic, double L) {
   double g = fmax(fmax(lo - x, x - hi), 0.0);
@@ -89,10 +138,12 @@ __device__ inline double axis_gap(double x, double lo, double hi, bool periodic,
 }
 
 // flags[q * n_own + k] = 1 when owned body k can be a neighbour of a body owned by the q-th peer: its centre lies within
-// S_k + S_max(peer) of that peer's bounding box (conservative; the exact predicate runs in the peer's link build).
-// Periodic boxes: centres are first wrapped into the unit cell (the boxes are those of wrapped centres).
+// S_k + S_max(peer) of that peer's bounding box AND of an occupied cell of that peer's occupancy grid (conservative; the
+// exact predicate runs in the peer's link build).
+// Periodic boxes: centres are first wrapped into the unit cell (the boxes and grids are those of wrapped centres).
 __global__ void __launch_bounds__(256)
-    select_for_peers_kernel(int64_t n_own, PeerList pl, RankBoxes rb, const double* __restrict__ center,
+    select_for_peers_kernel(int64_t n_own, PeerList pl, RankBoxes rb, OccGrid og,
+                            const unsigned long long* __restrict__ masks, const double* __restrict__ center,
                             const double* __restrict__ radius, const double* __restrict__ length,
                             const int32_t* __restrict__ kind, double buffer, Periodic P, uint32_t* __restrict__ flags) {
   const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -107,7 +158,9 @@ __global__ void __launch_bounds__(256)
   const double gy = axis_gap(c.y, rb.lo[r][1], rb.hi[r][1], P.on[1], P.L[1]);
   const double gz = axis_gap(c.z, rb.lo[r][2], rb.hi[r][2], P.on[2], P.L[2]);
   const bool empty = rb.lo[r][0] > rb.hi[r][0];
-  flags[t] = (!empty && gx <= reach && gy <= reach && gz <= reach) ? 1u : 0u;
+  bool near = !empty && gx <= reach && gy <= reach && gz <= reach;
+  if (near) near = occ_reaches(og, masks + static_cast<int64_t>(r) * og.words, c, reach, P);
+  flags[t] = near ? 1u : 0u;
 }
 
 __device__ inline void write_body_record(double* r, int64_t k, const double* __restrict__ center,
@@ -392,8 +445,37 @@ int dist_build(cudaStream_t st, mb200_neighbor_links* h, mb200_comm* comm, const
     n_global += own_of[r];
   }
   D.n_global = n_global;
+  // occupancy grids over the bounding box of all bodies (identical on every rank), all-gathered
+  OccGrid og;
+  double glo[3], ghi[3], extent = 0.0, smax_all = 0.0;
+  for (int r = 0; r < W; ++r) smax_all = std::max(smax_all, rb.smax[r]);
+  for (int d = 0; d < 3; ++d) {
+    double lo = 1.7976931348623157e308, hi = -1.7976931348623157e308;
+    for (int r = 0; r < W; ++r)
+      if (rb.lo[r][0] <= rb.hi[r][0]) lo = std::min(lo, rb.lo[r][d]), hi = std::max(hi, rb.hi[r][d]);
+    if (h->periodic.on[d]) lo = 0.0, hi = h->periodic.L[d];  // wrapped centres fill the unit cell
+    if (!(hi > lo)) lo = 0.0, hi = 1.0;
+    glo[d] = lo, ghi[d] = hi;
+    extent = std::max(extent, hi - lo);
+  }
+  og.G = 8;
+  if (smax_all > 0.0 && std::isfinite(extent / smax_all))
+    og.G = static_cast<int>(std::min<double>(kOccMaxG, std::max(8.0, std::ceil(extent / smax_all))));
+  og.words = (og.G * og.G * og.G + 63) / 64;
+  for (int d = 0; d < 3; ++d) {
+    og.lo[d] = glo[d];
+    og.inv_cell[d] = og.G / ((ghi[d] - glo[d]) * (1.0 + 1e-12));
+  }
+  Scratch<unsigned long long> occ;
+  MB200_TRY(occ.alloc(static_cast<size_t>(W + 1) * og.words, st));
+  MB200_CUDA(cudaMemsetAsync(occ.p, 0, og.words * sizeof(unsigned long long), st));
+  if (n_own > 0) {
+    occupancy_kernel<<<grid_for(n_own, 256), 256, 0, st>>>(n_own, og, bc, occ.p);
+    MB200_LAUNCHED();
+  }
+  MB200_NCCL(nccl->AllGather(occ.p, occ.p + og.words, og.words, ncclUint64, comm->comm, st));
 
-  pt.mark("1 boxes");
+  pt.mark("1 boxes + grids");
   // 2. which owned bodies does each peer need? one scan over (peer, owned body)
   PeerList pl;
   pl.npeers = D.npeers;
@@ -404,8 +486,8 @@ int dist_build(cudaStream_t st, mb200_neighbor_links* h, mb200_comm* comm, const
   MB200_TRY(gflags.alloc(m2 > 0 ? m2 : 1, st));
   MB200_TRY(gpos.alloc(m2 + 1, st));
   if (m2 > 0) {
-    select_for_peers_kernel<<<grid_for(m2, 256), 256, 0, st>>>(n_own, pl, rb, g->center, g->radius, g->length, g->kind,
-                                                              h->buffer, h->periodic, gflags.p);
+    select_for_peers_kernel<<<grid_for(m2, 256), 256, 0, st>>>(n_own, pl, rb, og, occ.p + og.words, g->center, g->radius,
+                                                              g->length, g->kind, h->buffer, h->periodic, gflags.p);
     MB200_LAUNCHED();
   }
   MB200_TRY(exclusive_scan_u32_to_i64(st, m2, gflags.p, gpos.p));
