@@ -292,10 +292,15 @@ __global__ void __launch_bounds__(256) boundary_flags_kernel(int64_t n, const in
   const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (b < n) flag[b] = push_ptr[b + 1] > push_ptr[b] ? 1u : 0u;
 }
+// ... and their class in owned_s: 0 ghost, 1 owned interior, 2 owned with ghost copies (one byte tells the body pass all)
 __global__ void __launch_bounds__(256) boundary_list_kernel(int64_t n, const uint32_t* __restrict__ flag,
-                                                            const int64_t* __restrict__ pos, uint32_t* __restrict__ list) {
+                                                            const int64_t* __restrict__ pos, uint32_t* __restrict__ list,
+                                                            uint8_t* __restrict__ owned_s) {
   const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (b < n && flag[b]) list[pos[b]] = static_cast<uint32_t>(b);
+  if (b < n && flag[b]) {
+    list[pos[b]] = static_cast<uint32_t>(b);
+    owned_s[b] = 2;
+  }
 }
 
 __global__ void __launch_bounds__(256) invert_perm_kernel(int64_t n, const uint32_t* __restrict__ perm,
@@ -687,7 +692,7 @@ int dist_build(cudaStream_t st, mb200_neighbor_links* h, mb200_comm* comm, const
     }
     MB200_TRY(exclusive_scan_u32_to_i64(st, nl, pcount.p, bpos.p));
     if (nl > 0) {
-      boundary_list_kernel<<<grid_for(nl, 256), 256, 0, st>>>(nl, pcount.p, bpos.p, D.boundary.p);
+      boundary_list_kernel<<<grid_for(nl, 256), 256, 0, st>>>(nl, pcount.p, bpos.p, D.boundary.p, D.owned_s.p);
       MB200_LAUNCHED();
     }
     int64_t nb = 0;

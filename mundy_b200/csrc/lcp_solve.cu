@@ -280,7 +280,11 @@ constexpr int kChunk = MB200_BODY_CHUNK;
 // A thread per body. Its incidence entries are taken kChunk at a time: entry words, then the active bits, then the
 // records of the active ones are each loaded as a group of independent requests before their first use, and the
 // contributions are added in entry order.
-template <int ARM, int MODE, bool FINAL>
+// (Forcing more resident CTAs through __launch_bounds__ loses: 9 CTAs / 56 registers 79 us, 11 / 40 registers 123 us
+// against 66 us at ptxas' own 72 registers: the spills go through the same load/store path as the gathers.)
+// HALO: the peer-memory multi-GPU form (ownership classes, boundary bodies first, remote stores, early halo flag); a
+// template parameter so that the single-GPU kernel does not carry its registers (72 against 92).
+template <int ARM, int MODE, bool FINAL, bool HALO>
 __global__ void __launch_bounds__(kBodyThreads)
     body_pass_kernel(LcpArgs a, int first, double* __restrict__ F, double* __restrict__ T, double* __restrict__ U,
                      double* __restrict__ W, const double* __restrict__ U_ext, const double* __restrict__ W_ext) {
@@ -297,7 +301,7 @@ __global__ void __launch_bounds__(kBodyThreads)
   const double* sigp = reinterpret_cast<const double*>(a.sig);
   double speed = 0.0;
   // peer mode: work items [0, nb_pad) are the boundary bodies (padded to whole CTAs), the rest all bodies
-  const bool halo = !FINAL && a.push_ptr != nullptr;
+  constexpr bool halo = HALO && !FINAL;
   const int64_t nb_ctas = halo ? (a.n_boundary + kBodyThreads - 1) / kBodyThreads : 0;
   const int64_t nb_pad = nb_ctas * kBodyThreads;
 
@@ -318,10 +322,10 @@ __global__ void __launch_bounds__(kBodyThreads)
     unsigned long long m0, m1;  // the body's active bits: one load, independent of the pointers
     asm("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(m0), "=l"(m1) : "l"(a.bmask + 2 * b));
     int64_t pk = 0, pke = 0;
-    uint8_t own = 1;
-    if (halo) pk = __ldg(a.push_ptr + b), pke = __ldg(a.push_ptr + b + 1);
-    if (!FINAL && a.owned) own = __ldg(a.owned + b);
-    if (wi >= nb_pad && pke > pk) continue;  // has ghost copies: done by a boundary CTA
+    uint8_t own = 1;  // peer mode: 0 ghost, 1 owned, 2 owned with ghost copies on other ranks
+    if (halo && wi < nb_pad) pk = __ldg(a.push_ptr + b), pke = __ldg(a.push_ptr + b + 1);
+    if (halo) own = __ldg(a.owned + b);
+    if (halo && wi >= nb_pad && own == 2) continue;  // has ghost copies: done by a boundary CTA
     // peer mode: ghost rows belong to their owners, who store into them from their own GPUs
     if (!own) continue;
     double acc[NC];
@@ -646,6 +650,7 @@ __device__ inline bool rate_contact(const LcpArgs& a, int64_t c, const double2& 
 // (about 84 of the 106 wavefronts a warp issues per 32 contacts), which the bulk copies do not relieve, and eight warps
 // released together by one barrier issue their gathers in bursts: 78 us against 66 us. The plain form is the default;
 // MB200_RATE_PIPELINE=bulk selects the staged one.
+// (64 registers, four CTAs per SM. Five CTAs / 48 registers: 78 us, six / 40 registers: 88 us against 63 us: spills.)
 template <int ARM, int MODE, bool PEER, bool BULK>
 __global__ void __launch_bounds__(kRateThreads) rate_pass_kernel(LcpArgs a, int it, int first) {
   if (a.state_blk->done) return;
@@ -843,12 +848,17 @@ int resident_grid(K kernel, int threads) {
 template <int ARM>
 void launch_body(const LcpArgs& a, int grid, cudaStream_t st, int mode, bool fin_pass, int first, double* F, double* T,
                  double* U, double* W) {
+  const bool halo = a.push_ptr != nullptr;
   if (fin_pass)
-    body_pass_kernel<ARM, 0, true><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
+    body_pass_kernel<ARM, 0, true, false><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
+  else if (mode == 0 && halo)
+    body_pass_kernel<ARM, 0, false, true><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
   else if (mode == 0)
-    body_pass_kernel<ARM, 0, false><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
+    body_pass_kernel<ARM, 0, false, false><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
+  else if (halo)
+    body_pass_kernel<ARM, 1, false, true><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
   else
-    body_pass_kernel<ARM, 1, false><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
+    body_pass_kernel<ARM, 1, false, false><<<grid, kBodyThreads, 0, st>>>(a, first, F, T, U, W, nullptr, nullptr);
 }
 bool rate_pipeline_bulk() {
   static const bool bulk = [] {
