@@ -178,15 +178,25 @@ def test_periodic_step_converged_overlap_removed(cuda):
     assert across.any() and phi[across].min() >= -10 * tol  # links through the boundary were resolved as well
 
 
-def test_periodic_rejected_on_multi_gpu_path(cuda):
-    """The distributed step refuses a periodic box (status MB200_ERR_INVALID_ARGUMENT) instead of silently treating it
-    as free space."""
+def test_periodic_box_on_the_distributed_path(cuda):
+    """A periodic box through the distributed step (refused in round 1). With one rank it must equal the single-GPU
+    periodic step bit for bit; 2 / 4 / 8 ranks are covered by tests/test_gpu_dist.py (periodic spheres case)."""
     from mundy_b200 import dist as mbd
     from mundy_b200 import ops
-    from mundy_b200._capi import Mb200Error
-    w = wl.polydisperse_spheres(2000, phi=0.25)
-    b = ops.make_bodies(dev(w["center"]), dev(w["radius"]))
-    links = ops.NeighborLinks().set_search_buffer(0.3).set_periodic([w["edge"]] * 3)
-    with pytest.raises(Mb200Error) as e:
-        mbd.step_dist(links, mbd.Comm(), b, 1e-3, 1e-4, 1e-5, 100)
-    assert e.value.status == -1 and "periodic" in str(e.value)
+    w = wl.polydisperse_spheres(3000, phi=0.3)
+    cell = [w["edge"]] * 3
+    out = []
+    for comm in (None, mbd.Comm()):
+        c = dev(w["center"])
+        b = ops.make_bodies(c, dev(w["radius"]))
+        links = ops.NeighborLinks().set_search_buffer(0.3).set_periodic(cell)
+        for _ in range(3):
+            if comm is None:
+                st = links.step(b, 1e-3, 1e-4, 1e-5, 10000, fixed_iters=6)
+            else:
+                st = mbd.step_dist(links, comm, b, 1e-3, 1e-4, 1e-5, 10000, fixed_iters=6)
+        out.append((host(c), st.num_links, st.lcp.max_abs_projected_sep, host(links.pairs())))
+    assert out[0][1] == out[1][1] and out[0][2] == out[1][2]
+    assert np.array_equal(out[0][3], out[1][3]) and np.array_equal(out[0][0], out[1][0])
+    free = oracle.search(w["center"], w["radius"] + 0.3)
+    assert out[1][1] > len(free)  # the periodic images add links on the distributed path too
