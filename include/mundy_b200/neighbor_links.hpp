@@ -30,6 +30,11 @@ namespace search_filters {
 enum class Kind { None = MB200_FILTER_NONE, ShapeDistance = MB200_FILTER_SHAPE_DISTANCE };
 }
 
+// Stand-ins for the two STK enumerations the reference's setters take (stk::topology::rank_t, stk::search::SearchMethod),
+// with the enumerators a caller of this path uses; the values are not STK's.
+enum class EntityRank { NODE_RANK, EDGE_RANK, FACE_RANK, ELEM_RANK };
+enum class SearchMethod { KDTREE, MORTON_LBVH, ARBORX };
+
 struct CollisionResult {  // scrap/lcp_spheres/KokkosLCP.cpp:667-671
   double max_abs_projected_sep;
   int ite_count;
@@ -48,6 +53,21 @@ class GenNeighborLinks {
   bool is_concretized() const { return concretized_; }
 
   // ---- setters (GenNeighborLinkers.hpp:401-462) ----
+  /// :409-418. Like the reference, only element-to-element searches are accepted.
+  GenNeighborLinks& set_source_target_rank(EntityRank source_rank, EntityRank target_rank) {
+    require_open("Cannot set source and target ranks after concretization.");
+    if (source_rank != EntityRank::ELEM_RANK || target_rank != EntityRank::ELEM_RANK)
+      throw std::runtime_error("To start, we will only support element to element neighbor searches.");
+    return *this;
+  }
+  /// :444-448. Stored; every method names the same candidate set (the fp64 predicate of SURVEY 8a-B2), which the device
+  /// finds with its own cell list whatever is asked for.
+  GenNeighborLinks& set_search_method(SearchMethod method) {
+    require_open("Cannot set search method after concretization.");
+    search_method_ = method;
+    return *this;
+  }
+  SearchMethod search_method() const { return search_method_; }
   GenNeighborLinks& set_enforce_source_target_symmetry(bool v) {
     require_open("Cannot set enforce source-target symmetry after concretization.");
     enforce_symmetry_ = v;  // stored, as in the reference (never consulted there either)
@@ -138,6 +158,7 @@ class GenNeighborLinks {
   Bodies bodies_;
   bool has_bodies_ = false, concretized_ = false;
   bool enforce_symmetry_ = false, allow_duplicates_ = false, sort_results_ = true;
+  SearchMethod search_method_ = SearchMethod::MORTON_LBVH;
   mb200_step_stats last_stats_{};
 };
 

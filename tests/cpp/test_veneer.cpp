@@ -181,7 +181,24 @@ int main() {
     mesh::Bodies bodies;
     bodies.n = 3, bodies.center = center.data(), bodies.radius = radius.data();
     mesh::GenNeighborLinks gen;
-    gen.set_search_buffer(0.0).set_sort_search_results(true).set_enforce_source_target_symmetry(true).acts_on(bodies).concretize();
+    gen.set_search_buffer(0.0).set_sort_search_results(true).set_enforce_source_target_symmetry(true)
+        .set_source_target_rank(mesh::EntityRank::ELEM_RANK, mesh::EntityRank::ELEM_RANK)
+        .set_search_method(mesh::SearchMethod::MORTON_LBVH);
+    bool rank_refused = false;  // GenNeighborLinkers.hpp:413-415: element-to-element only
+    try {
+      gen.set_source_target_rank(mesh::EntityRank::NODE_RANK, mesh::EntityRank::ELEM_RANK);
+    } catch (const std::runtime_error& e) {
+      rank_refused = std::strstr(e.what(), "element to element") != nullptr;
+    }
+    EXPECT_TRUE(rank_refused);
+    gen.acts_on(bodies).concretize();
+    bool method_refused = false;
+    try {
+      gen.set_search_method(mesh::SearchMethod::KDTREE);
+    } catch (const std::runtime_error& e) {
+      method_refused = std::strstr(e.what(), "after concretization") != nullptr;
+    }
+    EXPECT_TRUE(method_refused);
     bool threw = false;
     try {
       gen.set_search_buffer(1.0);
