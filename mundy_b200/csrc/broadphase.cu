@@ -9,6 +9,7 @@
 // The optional shape-distance search filter (GenNeighborLinkers.hpp:116-200 SearchFilter) is fused into the same passes.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <type_traits>
 #include <vector>
 
@@ -109,6 +110,39 @@ __global__ void __launch_bounds__(256) gather_records_kernel(int64_t n, const ui
 }
 
 // cell_range[key] = {start, end} over the sorted keys (table pre-zeroed: empty cells have start == end == 0).
+// A. AABB stage on the step's path: geom::compute_aabb(Spherocylinder) / (Sphere) (mundy/geom/src/mundy_geom/
+// compute_aabb.hpp:72-80,106-127: corners min/max(c -/+ d) -/+ r with d = (L/2)(q (x) z_hat) = the record's half-axis
+// vector), inflated by the search buffer and rounded OUTWARD to fp32: a conservative pre-reject for the shape-distance
+// filter. Two bodies whose surface separation is <= 2 * buffer have overlapping buffer-inflated capsules, hence
+// overlapping boxes; the outward fp32 rounding (>= 6e-8 relative) dwarfs the fp64 rounding of the separation itself.
+// The exact fp64 predicate and the exact shape distance stay the deciders. Record: {lo.xyz, hi.xyz, -, -} as 8 floats.
+__global__ void __launch_bounds__(256) box_records_kernel(int64_t n, const D4* __restrict__ b0, const D4* __restrict__ b1,
+                                                          double buffer, float4* __restrict__ box) {
+  const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const D4 c = ldg256(b0 + k), h = ldg256(b1 + k);
+  const double e = c.w + buffer;
+  const double ex = fabs(h.x) + e, ey = fabs(h.y) + e, ez = fabs(h.z) + e;
+  box[2 * k] = make_float4(__double2float_rd(c.x - ex), __double2float_rd(c.y - ey), __double2float_rd(c.z - ez),
+                           __double2float_ru(c.x + ex));
+  box[2 * k + 1] = make_float4(__double2float_ru(c.y + ey), __double2float_ru(c.z + ez), 0.f, 0.f);
+}
+struct Box6f {
+  float lx, ly, lz, hx, hy, hz;
+};
+__device__ inline Box6f load_box(const float4* box, int64_t k) {
+  const D4 r = ldg256(reinterpret_cast<const D4*>(box) + k);  // one 256-bit load
+  Box6f b;
+  b.lx = __int_as_float(__double2loint(r.x)), b.ly = __int_as_float(__double2hiint(r.x));
+  b.lz = __int_as_float(__double2loint(r.y)), b.hx = __int_as_float(__double2hiint(r.y));
+  b.hy = __int_as_float(__double2loint(r.z)), b.hz = __int_as_float(__double2hiint(r.z));
+  return b;
+}
+// closed intervals: touching counts (primitives/AABB.hpp:419-431)
+__device__ inline bool boxes_overlap(const Box6f& a, const Box6f& b) {
+  return !(a.hx < b.lx || b.hx < a.lx || a.hy < b.ly || b.hy < a.ly || a.hz < b.lz || b.hz < a.lz);
+}
+
 __global__ void __launch_bounds__(256) cell_ranges_kernel(int64_t n, const uint32_t* __restrict__ keys,
                                                           int2* __restrict__ cell_range) {
   const int64_t k = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -133,9 +167,12 @@ constexpr int kFindGroup = 8;  // consecutive bodies per warp in find_pairs_kern
 #ifndef MB200_FIND_MIN_CTAS
 #define MB200_FIND_MIN_CTAS 4  // 64 registers: four CTAs (32 warps) per SM; measured 4.70 / 3.98 / 3.67 ms per rebuild at 2 / 3 / 4
 #endif
-template <bool FILL, bool FILTER, bool PER>
+// BOX (shape filter, free space): the candidate walk tests the fp32 boxes above instead of the search spheres; the exact
+// sphere predicate moves to the queued survivors, in front of the shape distance.
+template <bool FILL, bool FILTER, bool PER, bool BOX>
 __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
-    find_pairs_kernel(int64_t n, const D4* __restrict__ sr, const D4* __restrict__ b0, const D4* __restrict__ b1,
+    find_pairs_kernel(int64_t n, const D4* __restrict__ sr, const float4* __restrict__ box, const D4* __restrict__ b0,
+                      const D4* __restrict__ b1,
                       const uint32_t* __restrict__ perm, const int2* __restrict__ cell_range, GridParams gp,
                       double cutoff, uint32_t* __restrict__ counts, const int64_t* __restrict__ rowptr,
                       int2* __restrict__ pairs, int32_t* __restrict__ slots, int slot_cap,
@@ -168,6 +205,8 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
     }
   }
   const D4 si = ldg256(sr + i);
+  Box6f bi{};
+  if (BOX) bi = load_box(box, i);
   // multi-GPU: links between two ghost bodies belong to other ranks
   const bool own_i = own ? own[i] != 0 : true;
   // (the shape filter's records of body i are re-read where they are used: one broadcast L1 hit per batch instead of 17
@@ -277,8 +316,11 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
       // order under divergence
       const bool fwd = pi < perm[j];
       const D4 a0 = fwd ? b0i : b0j, a1 = fwd ? b1i : b1j, c0 = fwd ? b0j : b0i, c1 = fwd ? b1j : b1i;
-      const PairGeom g = PER ? pair_geometry<true>(a0, a1, unwrap_to(P, a0, c0), c1) : pair_geometry<true>(a0, a1, c0, c1);
-      keep = g.sep <= cutoff;
+      // BOX: the survivor of the box test has not seen the exact candidate predicate yet
+      if (!BOX || is_candidate(si, ldg256(sr + j))) {
+        const PairGeom g = PER ? pair_geometry<true>(a0, a1, unwrap_to(P, a0, c0), c1) : pair_geometry<true>(a0, a1, c0, c1);
+        keep = g.sep <= cutoff;
+      }
     }
     emit(keep, j);
     // the qn - take < 64 remaining entries move to the front
@@ -295,11 +337,19 @@ __global__ void __launch_bounds__(256, MB200_FIND_MIN_CTAS)
     const int ca = candidate(t0), cb = candidate(t0 + 32);  // warp-wide: called by all lanes
     const int ja = (ta < total_cand) ? ca : -1;
     const int jb = (tb < total_cand) ? cb : -1;
-    D4 sa{0, 0, 0, 0}, sb{0, 0, 0, 0};
-    if (ja >= 0) sa = ldg256(sr + ja);
-    if (jb >= 0) sb = ldg256(sr + jb);
-    const bool ka = (ja >= 0) && (PER ? is_candidate_periodic(P, si, sa) : is_candidate(si, sa)) && (own_i || own[ja]);
-    const bool kb = (jb >= 0) && (PER ? is_candidate_periodic(P, si, sb) : is_candidate(si, sb)) && (own_i || own[jb]);
+    bool ka = false, kb = false;
+    if (BOX) {
+      if (ja >= 0) ka = boxes_overlap(bi, load_box(box, ja));
+      if (jb >= 0) kb = boxes_overlap(bi, load_box(box, jb));
+    } else {
+      D4 sa{0, 0, 0, 0}, sb{0, 0, 0, 0};
+      if (ja >= 0) sa = ldg256(sr + ja);
+      if (jb >= 0) sb = ldg256(sr + jb);
+      ka = (ja >= 0) && (PER ? is_candidate_periodic(P, si, sa) : is_candidate(si, sa));
+      kb = (jb >= 0) && (PER ? is_candidate_periodic(P, si, sb) : is_candidate(si, sb));
+    }
+    ka = ka && (own_i || own[ja]);
+    kb = kb && (own_i || own[jb]);
     if (FILTER) {
       const uint32_t ma = __ballot_sync(0xffffffffu, ka), mb = __ballot_sync(0xffffffffu, kb);
       if (ka) q[qn + __popc(ma & lt_mask)] = ja;
@@ -458,6 +508,9 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   MB200_TRY(radix_sort_u32(st, n, keys.p, keys_alt.p, h->perm.p, vals_alt.p, key_bits));
   gather_records_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, h->perm.p, sr.p, sr_s.p);
   MB200_LAUNCHED();
+  Scratch<float4> boxes;  // fp32 AABB pre-reject records (shape filter, free space)
+  static const bool box_off = getenv("MB200_NO_BOX_PREREJECT") != nullptr;
+  const bool use_box = filter && !h->periodic.any && !box_off;
   Scratch<uint8_t> own_s;  // ownership flags in Morton order (multi-GPU only)
   if (owned) {
     MB200_TRY(own_s.alloc(n, st));
@@ -471,6 +524,11 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
     MB200_TRY(h->ref_b1.reserve(n));
     MB200_TRY(b0c.alloc(n, st));
     MB200_TRY(pack_bodies(st, b, nullptr, b0c.p, h->ref_b1.p));
+    if (use_box) {
+      MB200_TRY(boxes.alloc(2 * static_cast<size_t>(n), st));
+      box_records_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, b0s.p, b1s.p, h->buffer, boxes.p);
+      MB200_LAUNCHED();
+    }
   }
 
   // 3. cell table
@@ -493,15 +551,16 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   auto launch_find = [&](auto fill_tag, const int64_t* rp, int2* out) {
     constexpr bool FILL = decltype(fill_tag)::value;
     uint32_t* cnt = FILL ? nullptr : counts.p;
-#define MB200_FIND(FILTER, PER)                                                                                      \
-  find_pairs_kernel<FILL, FILTER, PER><<<pgrid, 256, 0, st>>>(n, sr_s.p, FILTER ? b0s.p : nullptr,                   \
-                                                              FILTER ? b1s.p : nullptr, FILTER ? h->perm.p : nullptr, \
-                                                              cell_range.p, gp, cutoff, cnt, rp, out, slots.p,       \
-                                                              slot_cap, own_s.p, P)
+#define MB200_FIND(FILTER, PER, BOX)                                                                                 \
+  find_pairs_kernel<FILL, FILTER, PER, BOX><<<pgrid, 256, 0, st>>>(                                                  \
+      n, sr_s.p, boxes.p, FILTER ? b0s.p : nullptr, FILTER ? b1s.p : nullptr, FILTER ? h->perm.p : nullptr,          \
+      cell_range.p, gp, cutoff, cnt, rp, out, slots.p, slot_cap, own_s.p, P)
     if (filter) {
-      if (P.any) MB200_FIND(true, true); else MB200_FIND(true, false);
+      if (P.any) MB200_FIND(true, true, false);
+      else if (use_box) MB200_FIND(true, false, true);
+      else MB200_FIND(true, false, false);
     } else {
-      if (P.any) MB200_FIND(false, true); else MB200_FIND(false, false);
+      if (P.any) MB200_FIND(false, true, false); else MB200_FIND(false, false, false);
     }
 #undef MB200_FIND
   };
