@@ -209,6 +209,17 @@ int mb200_search_pairs_periodic(mb200_stream stream, int64_t n, const double* ce
 int mb200_narrow_phase_periodic(mb200_stream stream, const mb200_bodies* bodies, int64_t npairs, const int32_t* pairs,
                                 const double* cell_size_h, double* phi, double* normal, double* arm_i, double* arm_j);
 
+/* mb200_narrow_phase for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same arguments, same
+ * kernels and bit-identical results; the packed body records that mb200_narrow_phase keeps in stream-ordered scratch
+ * live in a static device array instead (4 MB, held by every GPU that loads the library until exit). The call makes no
+ * cudaMalloc / cudaMallocAsync / cudaFree and no allocating library call. bodies->n > MB200_NO_ALLOC_MAX_BODIES is
+ * refused with MB200_ERR_INVALID_ARGUMENT. Every call on a device shares the array: calls that overlap on the GPU
+ * (different streams) race; calls on one stream are ordered and safe. */
+#define MB200_NO_ALLOC_MAX_BODIES 65536
+int mb200_narrow_phase_no_alloc(mb200_stream stream, const mb200_bodies* bodies, int64_t npairs, const int32_t* pairs,
+                                double* phi, double* normal, double* arm_i, double* arm_j);
+
 /* Periodic metric leaves, batched (mundy/geom/src/mundy_geom/periodicity.hpp; every array [3n]; cell_size_h HOST[3]):
  *   sep[k]  = metric.sep(p1[k], p2[k])                          :814-818  minimum-image separation vector
  *   out[k]  = metric.wrap(p[k])                                 :821-824  into [0, L) per periodic axis

@@ -199,6 +199,16 @@ def narrow_phase(bodies, pairs, arms=False, cell_size=None):
     return phi, normal, ai, aj
 
 
+NO_ALLOC_MAX_BODIES = 65536  # MB200_NO_ALLOC_MAX_BODIES
+
+
+def narrow_phase_no_alloc(bodies, pairs, phi, normal, arm_i=None, arm_j=None):
+    """mb200_narrow_phase_no_alloc: the caller passes every output; the call allocates nothing (include/mundy_b200.h)."""
+    check(lib.mb200_narrow_phase_no_alloc(_stream(), C.byref(bodies), pairs.shape[0], _i32(pairs), _f64(phi),
+                                          _f64(normal), _f64(arm_i), _f64(arm_j)), "narrow_phase_no_alloc")
+    return phi, normal, arm_i, arm_j
+
+
 def search_pairs(center, search_radius, capacity=None, cell_size=None):
     n = search_radius.numel()
     count = C.c_int64(0)
