@@ -325,9 +325,11 @@ __global__ void __launch_bounds__(kBodyThreads)
     uint8_t own = 1;  // peer mode: 0 ghost, 1 owned, 2 owned with ghost copies on other ranks
     if (halo && wi < nb_pad) pk = __ldg(a.push_ptr + b), pke = __ldg(a.push_ptr + b + 1);
     if (halo) own = __ldg(a.owned + b);
-    if (halo && wi >= nb_pad && own == 2) continue;  // has ghost copies: done by a boundary CTA
-    // peer mode: ghost rows belong to their owners, who store into them from their own GPUs
-    if (!own) continue;
+    // peer mode: ghost rows belong to their owners, who store into them from their own GPUs; a body with ghost copies
+    // is done by a boundary CTA. Both are skipped by emptying the entry range (a select, not a branch on `own`: a
+    // branch here would hold the pointer and mask loads back until the flag byte has arrived, one more memory latency
+    // per body) and leave at the epilogue.
+    const bool skip = halo && (!own || (wi >= nb_pad && own == 2));
     double acc[NC];
 #pragma unroll
     for (int k = 0; k < NC; ++k) acc[k] = 0.0;
@@ -377,6 +379,7 @@ __global__ void __launch_bounds__(kBodyThreads)
     // mask's reach; every entry when the mask cannot be used.
     int64_t kover = beg + kMaskBits;
     if (!use_mask) m0 = 0, m1 = 0, kover = beg;
+    if (halo) m0 = skip ? 0ull : m0, m1 = skip ? 0ull : m1, kover = skip ? end : kover;
     auto next_pos = [&]() -> int64_t {
       if (m0) {
         const int64_t p = beg + (__ffsll(static_cast<long long>(m0)) - 1);
@@ -400,6 +403,7 @@ __global__ void __launch_bounds__(kBodyThreads)
     }
 
     // epilogue: U = M F; velocity records (and, multi-GPU, their ghost copies on the peers) or the solver's outputs
+    if (halo && skip) continue;
     if (!FINAL) {
       if (!any) {
         if (a.vzero[b]) continue;  // zero and known to be: nothing to rewrite
