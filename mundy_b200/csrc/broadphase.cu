@@ -387,28 +387,61 @@ constexpr int kTileBodies = 32;  // consecutive bodies per warp
 #define MB200_TILED_MIN_CTAS 4
 #endif
 
-// exact decision for one queued pair (shape filter): candidate predicate where the pre-reject was only the boxes, then
-// the shape distance in the caller's (i<j) order. One out-of-line copy: the distance code is ~3000 instructions.
-template <bool PER>
-struct PerArg {  // the periodic box travels by value, and only in the periodic instantiations
+// Per-warp working set in shared memory (the inner loop keeps only the candidate's record and a few counters in
+// registers; everything else lives here).
+struct TileWarp {
+  D4 rec[kTileBodies];       // per body of the warp: its box (BOX) or its search sphere
+  int pre[28], beg[28];      // the run's neighbour cells by ascending key: candidates in front of the cell, first body
+  int cnt[kTileBodies];      // FILTER: kept pairs so far, per body of the warp
+  int qj[64];                // FILTER: queued (body, j) awaiting the exact tests: a ring of 64
+  uint8_t qr[64];
+};
+// What the exact tests need, once per CTA (the out-of-line call takes one pointer instead of a dozen arguments).
+struct TileFilterArgs {
+  const D4 *sr, *b0, *b1;
+  const uint32_t* perm;
+  const int64_t* rowptr;
+  int2* pairs;
+  int32_t* slots;
+  double cutoff;
+  int slot_cap;
   Periodic P;
 };
-template <>
-struct PerArg<false> {};
-template <bool PER, bool BOX>
-__device__ __noinline__ bool filter_keeps(int64_t i, int j, const D4* __restrict__ sr, const D4* __restrict__ b0,
-                                          const D4* __restrict__ b1, const uint32_t* __restrict__ perm, double cutoff,
-                                          PerArg<PER> pa) {
-  if (j < 0) return false;
-  if (BOX && !is_candidate(ldg256(sr + i), ldg256(sr + j))) return false;
-  const D4 b0i = ldg256(b0 + i), b1i = ldg256(b1 + i);
-  const D4 b0j = ldg256(b0 + j), b1j = ldg256(b1 + j);
-  const bool fwd = __ldg(perm + i) < __ldg(perm + j);
-  const D4 a0 = fwd ? b0i : b0j, a1 = fwd ? b1i : b1j, c0 = fwd ? b0j : b0i, c1 = fwd ? b1j : b1i;
-  D4 c0u = c0;
-  if constexpr (PER) c0u = unwrap_to(pa.P, a0, c0);
-  const PairGeom g = pair_geometry<true>(a0, a1, c0u, c1);
-  return g.sep <= cutoff;
+
+// Exact decisions for `take` queued pairs from position qh of the ring (shape filter): the candidate predicate where
+// the pre-reject was only the boxes, then the shape distance in the caller's (i<j) order; kept pairs go to the body's
+// next positions (its running count + the rank among the kept lanes of the same body). Out of line: the distance code
+// is ~3000 instructions and there are two call sites; its registers are its own.
+template <bool FILL, bool PER, bool BOX>
+__device__ __noinline__ void filter_batch(TileWarp* w, const TileFilterArgs* fa, int i0, int qh, int take) {
+  const int lane = threadIdx.x & 31;
+  int j = -1, r = 32 + lane;  // idle lanes: distinct body tags
+  if (lane < take) {
+    const int slot = (qh + lane) & 63;
+    j = w->qj[slot];
+    r = w->qr[slot];
+  }
+  const int i = i0 + (r & 31);
+  bool keep = false;
+  if (j >= 0 && (!BOX || is_candidate(ldg256(fa->sr + i), ldg256(fa->sr + j)))) {
+    const D4 b0i = ldg256(fa->b0 + i), b1i = ldg256(fa->b1 + i);
+    const D4 b0j = ldg256(fa->b0 + j), b1j = ldg256(fa->b1 + j);
+    const bool fwd = __ldg(fa->perm + i) < __ldg(fa->perm + j);
+    const D4 a0 = fwd ? b0i : b0j, a1 = fwd ? b1i : b1j, c0 = fwd ? b0j : b0i, c1 = fwd ? b1j : b1i;
+    D4 c0u = c0;
+    if constexpr (PER) c0u = unwrap_to(fa->P, a0, c0);
+    keep = pair_geometry<true>(a0, a1, c0u, c1).sep <= fa->cutoff;
+  }
+  const uint32_t grp = __match_any_sync(0xffffffffu, r);
+  const uint32_t km = __ballot_sync(0xffffffffu, keep) & grp;
+  const int pos = w->cnt[r & 31] + __popc(km & ((1u << lane) - 1u));
+  if (keep) {
+    if (FILL) fa->pairs[fa->rowptr[i] + pos] = make_int2(i, j);
+    else if (pos < fa->slot_cap) fa->slots[static_cast<int64_t>(i) * fa->slot_cap + pos] = j;
+  }
+  __syncwarp();
+  if (keep && (km >> lane) == 1u) w->cnt[r] = pos + 1;  // the last kept lane of the body
+  __syncwarp();
 }
 
 template <bool FILL, bool FILTER, bool PER, bool BOX>
@@ -418,43 +451,47 @@ __global__ void __launch_bounds__(256, MB200_TILED_MIN_CTAS)
                             const int2* __restrict__ cell_range, GridParams gp, double cutoff,
                             uint32_t* __restrict__ counts, const int64_t* __restrict__ rowptr, int2* __restrict__ pairs,
                             int32_t* __restrict__ slots, int slot_cap, const uint8_t* __restrict__ own, Periodic P) {
+  __shared__ __align__(32) TileWarp s_warp[8];
+  __shared__ TileFilterArgs s_fa;
+  if (FILTER) {
+    if (threadIdx.x == 0) {
+      s_fa.sr = sr, s_fa.b0 = b0, s_fa.b1 = b1, s_fa.perm = perm, s_fa.rowptr = rowptr, s_fa.pairs = pairs;
+      s_fa.slots = slots, s_fa.cutoff = cutoff, s_fa.slot_cap = slot_cap, s_fa.P = P;
+    }
+    __syncthreads();
+  }
   const int lane = threadIdx.x & 31;
-  const int wib = threadIdx.x >> 5;
+  TileWarp* w = &s_warp[threadIdx.x >> 5];
   const int64_t i_begin = ((static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5) * kTileBodies;
   if (i_begin >= n) return;
+  const int i0 = static_cast<int>(i_begin);  // body indices fit an int (pair lists hold ints)
   const int nb = static_cast<int>(min(static_cast<int64_t>(kTileBodies), n - i_begin));  // bodies of this warp
   const uint32_t lt_mask = (1u << lane) - 1u;
-  __shared__ int s_pre[8][28], s_beg[8][28];
-  __shared__ __align__(32) D4 s_rec[8][kTileBodies];  // per body of the warp: its box (BOX) or its search sphere
-  __shared__ int s_cnt[8][kTileBodies];               // FILTER: kept pairs so far, per body of the warp
-  __shared__ int s_qj[FILTER ? 8 : 1][FILTER ? 64 : 1];
-  __shared__ uint8_t s_qr[FILTER ? 8 : 1][FILTER ? 64 : 1];
-  int* wpre = s_pre[wib];
-  int* wbeg = s_beg[wib];
-  const D4* wrec = s_rec[wib];
-  int* wcnt = s_cnt[wib];
 
   // the warp's bodies: search sphere -> cell; records into shared memory
-  const int64_t my_i = i_begin + lane;
   const bool have = lane < nb;
-  D4 s_mine{0, 0, 0, 0};
-  if (have) s_mine = ldg256(sr + my_i);
-  const int mcx = have ? cell_coord(s_mine.x, gp, 0) : 0;
-  const int mcy = have ? cell_coord(s_mine.y, gp, 1) : 0;
-  const int mcz = have ? cell_coord(s_mine.z, gp, 2) : 0;
-  const uint32_t mkey = have ? morton3(mcx, mcy, mcz) : 0xffffffffu;
-  if (have) s_rec[wib][lane] = BOX ? ldg256(reinterpret_cast<const D4*>(box) + my_i) : s_mine;
-  wcnt[lane] = 0;
-  const bool own_mine = (own && have) ? own[my_i] != 0 : true;
-  const uint32_t own_bits = __ballot_sync(0xffffffffu, own_mine);
+  uint32_t mkey = 0xffffffffu, mcell = 0;  // Morton key and packed cell coordinates of this lane's body
+  {
+    D4 s_mine{0, 0, 0, 0};
+    if (have) {
+      s_mine = ldg256(sr + i0 + lane);
+      const int cx = cell_coord(s_mine.x, gp, 0), cy = cell_coord(s_mine.y, gp, 1), cz = cell_coord(s_mine.z, gp, 2);
+      mkey = morton3(cx, cy, cz);
+      mcell = static_cast<uint32_t>(cx) | (static_cast<uint32_t>(cy) << 10) | (static_cast<uint32_t>(cz) << 20);
+      w->rec[lane] = BOX ? ldg256(reinterpret_cast<const D4*>(box) + i0 + lane) : s_mine;
+    }
+  }
+  w->cnt[lane] = 0;
+  // multi-GPU: bit r set = body r of the warp is owned (links between two ghosts belong to other ranks)
+  const uint32_t own_bits = own ? __ballot_sync(0xffffffffu, have && own[i0 + lane] != 0) : 0xffffffffu;
   // FILL: bodies whose pairs the count pass cached are copied; the others are found again
   uint32_t todo = __ballot_sync(0xffffffffu, have);
   int64_t my_out = 0;
   if (FILL) {
     int cnt = 0;
     if (have) {
-      my_out = rowptr[my_i];
-      cnt = static_cast<int>(rowptr[my_i + 1] - my_out);
+      my_out = rowptr[i0 + lane];
+      cnt = static_cast<int>(rowptr[i0 + lane + 1] - my_out);
     }
     todo = __ballot_sync(0xffffffffu, have && cnt > slot_cap);
     for (int r = 0; r < nb; ++r) {
@@ -466,163 +503,164 @@ __global__ void __launch_bounds__(256, MB200_TILED_MIN_CTAS)
     }
     if (todo == 0) return;
   }
-  const uint32_t prev_key = __shfl_up_sync(0xffffffffu, mkey, 1);
-  uint32_t heads = __ballot_sync(0xffffffffu, have && (lane == 0 || prev_key != mkey));
+  uint32_t heads;
+  {
+    const uint32_t prev_key = __shfl_up_sync(0xffffffffu, mkey, 1);
+    heads = __ballot_sync(0xffffffffu, have && (lane == 0 || prev_key != mkey));
+  }
   __syncwarp();
 
-  int qn = 0, qh = 0;  // FILTER: queue length and head (ring of 64)
+  int qn = 0, qh = 0;  // FILTER: queue length and head
   int mycnt = 0;       // !FILTER: kept pairs of the body this lane stands for
-  auto evaluate = [&](int take) {
-    int j = -1, r = 32 + lane;  // idle lanes: distinct body tags
-    if (FILTER && lane < take) {
-      const int slot = (qh + lane) & 63;
-      j = s_qj[FILTER ? wib : 0][FILTER ? slot : 0];
-      r = s_qr[FILTER ? wib : 0][FILTER ? slot : 0];
-    }
-    const int64_t i = i_begin + (r & 31);
-    PerArg<PER> pa;
-    if constexpr (PER) pa.P = P;
-    const bool keep = filter_keeps<PER, BOX>(i, j, sr, b0, b1, perm, cutoff, pa);
-    const uint32_t grp = __match_any_sync(0xffffffffu, r);
-    const uint32_t km = __ballot_sync(0xffffffffu, keep) & grp;
-    const int pos = wcnt[r & 31] + __popc(km & lt_mask);
-    if (keep) {
-      if (FILL) pairs[rowptr[i] + pos] = make_int2(static_cast<int>(i), j);
-      else if (pos < slot_cap) slots[i * slot_cap + pos] = j;
-    }
-    __syncwarp();
-    if (keep && (km >> lane) == 1u) wcnt[r] = pos + 1;  // the last kept lane of the body
-    __syncwarp();
-    qh = (qh + take) & 63;
-    qn -= take;
-  };
 
   while (heads) {
     const int ra = __ffs(heads) - 1;
     heads &= heads - 1;
     const int rb = heads ? __ffs(heads) - 1 : nb;  // run = bodies [ra, rb) of the warp: one cell
-    const uint32_t run_mask = ((rb >= 32) ? 0xffffffffu : ((1u << rb) - 1u)) & ~((1u << ra) - 1u);
-    if (FILL && !(todo & run_mask)) continue;
-    const int64_t base_i = i_begin + ra;
-    const int cx = __shfl_sync(0xffffffffu, mcx, ra), cy = __shfl_sync(0xffffffffu, mcy, ra),
-              cz = __shfl_sync(0xffffffffu, mcz, ra);
+    // bodies of the run that are searched (FILL: only those the count pass could not cache)
+    const uint32_t run_bits = ((rb >= 32) ? 0xffffffffu : ((1u << rb) - 1u)) & ~((1u << ra) - 1u) & todo;
+    if (run_bits == 0) continue;
+    const int base_i = i0 + ra;
     const uint32_t my_key = __shfl_sync(0xffffffffu, mkey, ra);
-    // table of the neighbour cells with key >= own key: lane l < 27 owns cell l (as in the walk above)
-    uint32_t nkey = 0xffffffffu;
-    int beg = 0, len = 0;
-    if (lane < 27) {
-      int x = cx + (lane % 3) - 1, y = cy + ((lane / 3) % 3) - 1, z = cz + (lane / 9) - 1;
-      bool inside = true;
-      if (PER) {
-        const int off[3] = {(lane % 3) - 1, ((lane / 3) % 3) - 1, (lane / 9) - 1};
-        int* xyz[3] = {&x, &y, &z};
+    int total_cand, nvalid;
+    {
+      // table of the neighbour cells with key >= own key: lane l < 27 owns cell l (as in the walk above)
+      const uint32_t cc = __shfl_sync(0xffffffffu, mcell, ra);
+      const int cx = cc & 1023u, cy = (cc >> 10) & 1023u, cz = cc >> 20;
+      uint32_t nkey = 0xffffffffu;
+      int beg = 0, len = 0;
+      if (lane < 27) {
+        int x = cx + (lane % 3) - 1, y = cy + ((lane / 3) % 3) - 1, z = cz + (lane / 9) - 1;
+        bool inside = true;
+        if (PER) {
+          const int off[3] = {(lane % 3) - 1, ((lane / 3) % 3) - 1, (lane / 9) - 1};
+          int* xyz[3] = {&x, &y, &z};
 #pragma unroll
-        for (int d = 0; d < 3; ++d) {
-          if (gp.per[d]) {
-            inside = inside && (off[d] == 0 || (off[d] < 0 ? gp.nc[d] >= 2 : gp.nc[d] >= 3));
-            *xyz[d] = (*xyz[d] + gp.nc[d]) % gp.nc[d];
+          for (int d = 0; d < 3; ++d) {
+            if (gp.per[d]) {
+              inside = inside && (off[d] == 0 || (off[d] < 0 ? gp.nc[d] >= 2 : gp.nc[d] >= 3));
+              *xyz[d] = (*xyz[d] + gp.nc[d]) % gp.nc[d];
+            }
+          }
+        }
+        if (inside && x >= 0 && y >= 0 && z >= 0 && x < gp.nc[0] && y < gp.nc[1] && z < gp.nc[2]) {
+          const uint32_t k = morton3(x, y, z);
+          if (k >= my_key) {
+            const int2 rg = __ldg(cell_range + k);
+            beg = (k == my_key) ? base_i + 1 : rg.x;
+            len = rg.y - beg;
+            if (len > 0 || k == my_key) nkey = k;
+            if (len < 0) len = 0;
           }
         }
       }
-      if (inside && x >= 0 && y >= 0 && z >= 0 && x < gp.nc[0] && y < gp.nc[1] && z < gp.nc[2]) {
-        const uint32_t k = morton3(x, y, z);
-        if (k >= my_key) {
-          const int2 rg = __ldg(cell_range + k);
-          beg = (k == my_key) ? static_cast<int>(base_i) + 1 : rg.x;
-          len = rg.y - beg;
-          if (len > 0 || k == my_key) nkey = k;
-          if (len < 0) len = 0;
+      const bool valid = nkey != 0xffffffffu;
+      int rank = 0, pre = 0;
+#pragma unroll
+      for (int m = 0; m < 27; ++m) {
+        const uint32_t km = __shfl_sync(0xffffffffu, nkey, m);
+        const int lm = __shfl_sync(0xffffffffu, len, m);
+        if (km < nkey) {
+          rank += 1;
+          pre += lm;
         }
       }
-    }
-    const bool valid = nkey != 0xffffffffu;
-    int rank = 0, pre = 0;
-#pragma unroll
-    for (int m = 0; m < 27; ++m) {
-      const uint32_t km = __shfl_sync(0xffffffffu, nkey, m);
-      const int lm = __shfl_sync(0xffffffffu, len, m);
-      if (km < nkey) {
-        rank += 1;
-        pre += lm;
+      nvalid = __popc(__ballot_sync(0xffffffffu, valid));
+      __syncwarp();  // the previous run's table is no longer read
+      if (valid) {
+        w->pre[rank] = pre;
+        w->beg[rank] = beg;
       }
-    }
-    const int nvalid = __popc(__ballot_sync(0xffffffffu, valid));
-    __syncwarp();
-    if (valid) {
-      wpre[rank] = pre;
-      wbeg[rank] = beg;
-    }
-    int total_cand = valid ? pre + len : 0;
+      total_cand = valid ? pre + len : 0;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) total_cand = max(total_cand, __shfl_xor_sync(0xffffffffu, total_cand, o));
-    __syncwarp();
-    const int rpre = (lane == 0) ? 0 : ((lane < nvalid) ? wpre[lane] : 0x7fffffff);
+      for (int o = 16; o > 0; o >>= 1) total_cand = max(total_cand, __shfl_xor_sync(0xffffffffu, total_cand, o));
+      __syncwarp();
+    }
+    const int rpre = (lane == 0) ? 0 : ((lane < nvalid) ? w->pre[lane] : 0x7fffffff);
 
     for (int t0 = 0; t0 < total_cand; t0 += 32) {
-      // flattened index t0 + lane -> body j (one look-up per tile)
-      int j = -1;
-      {
-        const uint32_t below = __ballot_sync(0xffffffffu, rpre <= t0);
-        const int rel = rpre - t0;
-        const uint32_t starts = __reduce_or_sync(0xffffffffu, (rel > 0 && rel < 32) ? (1u << rel) : 0u);
-        const int lo = __popc(below) - 1 + __popc(starts & ((2u << lane) - 1u));
-        const int pre_lo = (lo == 0) ? 0 : wpre[lo];
-        const int beg_lo = (lo == 0) ? static_cast<int>(base_i) + 1 : wbeg[lo];
-        if (t0 + lane < total_cand) j = beg_lo + (t0 + lane - pre_lo);
-      }
-      Box6f bj{};
-      D4 sj{0, 0, 0, 0};
-      bool own_j = true;
-      if (j >= 0) {
-        if (BOX) bj = load_box(box, j);
-        else sj = ldg256(sr + j);
-        if (own) own_j = own[j] != 0;
-      }
-      const int64_t jj = (j >= 0) ? j : -1;
-      for (int r = ra; r < rb; ++r) {
-        if (FILL && !((todo >> r) & 1u)) continue;
-        const int64_t i = i_begin + r;
-        bool hit = jj > i && (own_j || ((own_bits >> r) & 1u));
-        if (BOX) {
-          const D4 rec = wrec[r];  // broadcast
-          Box6f bi;
-          bi.lx = __int_as_float(__double2loint(rec.x)), bi.ly = __int_as_float(__double2hiint(rec.x));
-          bi.lz = __int_as_float(__double2loint(rec.y)), bi.hx = __int_as_float(__double2hiint(rec.y));
-          bi.hy = __int_as_float(__double2loint(rec.z)), bi.hz = __int_as_float(__double2hiint(rec.z));
-          hit = hit && boxes_overlap(bi, bj);
-        } else {
-          const D4 si = wrec[r];
-          hit = hit && (PER ? is_candidate_periodic(P, si, sj) : is_candidate(si, sj));
+      uint32_t pending = run_bits;  // bodies of the run still to meet this tile
+      do {
+        // The tile: flattened index t0 + lane -> body j, its record, and the bodies of the warp it may pair with (those
+        // in front of it: only the own cell's candidates can fail i < j; for a ghost candidate, the owned ones).
+        // Computed again after a batch of exact tests, so that none of it has to survive the call.
+        int j = -1;
+        {
+          const uint32_t below = __ballot_sync(0xffffffffu, rpre <= t0);
+          const int rel = rpre - t0;
+          const uint32_t starts = __reduce_or_sync(0xffffffffu, (rel > 0 && rel < 32) ? (1u << rel) : 0u);
+          const int lo = __popc(below) - 1 + __popc(starts & ((2u << lane) - 1u));
+          const int pre_lo = (lo == 0) ? 0 : w->pre[lo];
+          const int beg_lo = (lo == 0) ? base_i + 1 : w->beg[lo];
+          if (t0 + lane < total_cand) j = beg_lo + (t0 + lane - pre_lo);
         }
-        const uint32_t m = __ballot_sync(0xffffffffu, hit);
-        if (m == 0) continue;
-        if (FILTER) {
-          if (hit) {
-            const int slot = (qh + qn + __popc(m & lt_mask)) & 63;
-            s_qj[FILTER ? wib : 0][FILTER ? slot : 0] = j;
-            s_qr[FILTER ? wib : 0][FILTER ? slot : 0] = static_cast<uint8_t>(r);
+        Box6f bj{};
+        D4 sj{0, 0, 0, 0};
+        uint32_t allow = 0;
+        if (j >= 0) {
+          if (BOX) bj = load_box(box, j);
+          else sj = ldg256(sr + j);
+          const int ahead = j - i0;  // bodies [0, ahead) of the warp precede j
+          allow = (ahead >= 32) ? 0xffffffffu : ((1u << ahead) - 1u);
+          if (own && !own[j]) allow &= own_bits;
+        }
+        allow &= pending;
+        uint32_t rbits = __reduce_or_sync(0xffffffffu, allow);  // bodies some candidate of the tile may pair with
+        pending = 0;
+        while (rbits) {
+          const int r = __ffs(rbits) - 1;
+          rbits &= rbits - 1;
+          bool hit = (allow >> r) & 1u;
+          if (BOX) {
+            const D4 rec = w->rec[r];  // broadcast
+            Box6f bi;
+            bi.lx = __int_as_float(__double2loint(rec.x)), bi.ly = __int_as_float(__double2hiint(rec.x));
+            bi.lz = __int_as_float(__double2loint(rec.y)), bi.hx = __int_as_float(__double2hiint(rec.y));
+            bi.hy = __int_as_float(__double2loint(rec.z)), bi.hz = __int_as_float(__double2hiint(rec.z));
+            hit = hit && boxes_overlap(bi, bj);
+          } else {
+            const D4 si = w->rec[r];
+            hit = hit && (PER ? is_candidate_periodic(P, si, sj) : is_candidate(si, sj));
           }
-          qn += __popc(m);
+          const uint32_t m = __ballot_sync(0xffffffffu, hit);
+          if (m == 0) continue;
+          if (FILTER) {
+            if (hit) {
+              const int slot = (qh + qn + __popc(m & lt_mask)) & 63;
+              w->qj[slot] = j;
+              w->qr[slot] = static_cast<uint8_t>(r);
+            }
+            qn += __popc(m);
+            if (qn >= 32) {  // a full batch: leave the tile, run the exact tests, come back for the other bodies
+              pending = rbits;
+              break;
+            }
+          } else {
+            const int base = __shfl_sync(0xffffffffu, mycnt, r);
+            const int64_t out_r = FILL ? __shfl_sync(0xffffffffu, my_out, r) : 0;
+            if (hit) {
+              const int pos = base + __popc(m & lt_mask);
+              if (FILL) pairs[out_r + pos] = make_int2(i0 + r, j);
+              else if (pos < slot_cap) slots[static_cast<int64_t>(i0 + r) * slot_cap + pos] = j;
+            }
+            if (lane == r) mycnt += __popc(m);
+          }
+        }
+        if (FILTER && qn >= 32) {
           __syncwarp();
-          if (qn >= 32) evaluate(32);
-        } else {
-          const int base = __shfl_sync(0xffffffffu, mycnt, r);
-          const int64_t out_r = FILL ? __shfl_sync(0xffffffffu, my_out, r) : 0;
-          if (hit) {
-            const int pos = base + __popc(m & lt_mask);
-            if (FILL) pairs[out_r + pos] = make_int2(static_cast<int>(i), j);
-            else if (pos < slot_cap) slots[i * slot_cap + pos] = j;
-          }
-          if (lane == r) mycnt += __popc(m);
+          filter_batch<FILL, PER, BOX>(w, &s_fa, i0, qh, 32);
+          qh = (qh + 32) & 63;
+          qn -= 32;
         }
-      }
+      } while (pending);
     }
   }
   if (FILTER) {
-    while (qn > 0) evaluate(min(qn, 32));
-    if (!FILL && have) counts[my_i] = static_cast<uint32_t>(wcnt[lane]);
+    __syncwarp();
+    if (qn > 0) filter_batch<FILL, PER, BOX>(w, &s_fa, i0, qh, qn);
+    if (!FILL && have) counts[i0 + lane] = static_cast<uint32_t>(w->cnt[lane]);
   } else {
-    if (!FILL && have) counts[my_i] = static_cast<uint32_t>(mycnt);
+    if (!FILL && have) counts[i0 + lane] = static_cast<uint32_t>(mycnt);
   }
 }
 
