@@ -888,8 +888,8 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
     launch_find(std::true_type{}, rowptr.p, out);
     MB200_LAUNCHED();
   }
-  // 5. body-major incidence lists for the contact operator
-  return build_incidence(st, n, total, h->pairs.p, &h->inc);
+  // 5. body-major incidence lists for the contact operator (the list is sorted by (i, j) and its rows are known)
+  return build_incidence_sorted(st, n, total, h->pairs.p, rowptr.p, &h->inc);
 }
 
 // Device flag (h->flag) = 1 when some body moved more than half the buffer since the last build. No host sync.

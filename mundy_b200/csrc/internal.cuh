@@ -22,6 +22,9 @@ struct Incidence {
   Scratch<int32_t> bad;    // 1: some pair named a body outside [0, n)
 };
 int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, Incidence* inc);
+// The same lists without a sort, for a pair list sorted by (i, j), i < j, with row pointers rowptr[n + 1] (the link build).
+int build_incidence_sorted(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, const int64_t* rowptr,
+                           Incidence* inc);
 int check_incidence(cudaStream_t st, const Incidence& inc);  // synchronises; error if `bad` was raised
 
 // The BBPGD solve on contact records (layout: lcp_solve.cu header). rec is modified when U_ext != NULL (phi0 correction).

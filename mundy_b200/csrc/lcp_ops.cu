@@ -136,6 +136,113 @@ int build_incidence(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* p
   return MB200_OK;
 }
 
+// The same lists for a pair list that is sorted by (i, j) with i < j and whose row pointers are known (the link build's
+// own output): no sort. In ascending (contact, side) order a body's entries are first the contacts in which it is the
+// SECOND body (they belong to rows i < b, hence to smaller contact indices), then its own row, which is contiguous. The
+// row part is placed directly; the second-body part is claimed slot by slot with an atomic counter and then put in
+// ascending order per body (a few entries each), so the result does not depend on the order of the atomics.
+namespace {
+
+__global__ void __launch_bounds__(256) second_counts_kernel(int64_t npairs, const int2* __restrict__ pairs,
+                                                            uint32_t* __restrict__ jcount) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c < npairs) atomicAdd(jcount + pairs[c].y, 1u);
+}
+__global__ void __launch_bounds__(256) degree_kernel(int64_t n, const int64_t* __restrict__ rowptr,
+                                                     const uint32_t* __restrict__ jcount, uint32_t* __restrict__ deg) {
+  const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (b < n) deg[b] = jcount[b] + static_cast<uint32_t>(rowptr[b + 1] - rowptr[b]);
+}
+__global__ void __launch_bounds__(256)
+    incidence_fill_kernel(int64_t npairs, const int2* __restrict__ pairs, const int64_t* __restrict__ rowptr,
+                          const int64_t* __restrict__ ptr, const uint32_t* __restrict__ jcount,
+                          uint32_t* __restrict__ jfill, uint32_t* __restrict__ list, uint32_t* __restrict__ epos) {
+  const int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (c >= npairs) return;
+  const int2 p = pairs[c];
+  const int64_t pos_i = ptr[p.x] + jcount[p.x] + (c - rowptr[p.x]);
+  list[pos_i] = static_cast<uint32_t>(2 * c);
+  epos[2 * c] = static_cast<uint32_t>(pos_i);
+  list[ptr[p.y] + atomicAdd(jfill + p.y, 1u)] = static_cast<uint32_t>(2 * c + 1);
+}
+// ascending order of a body's second-body entries (insertion sort; heap sort for long lists), then their positions
+__global__ void __launch_bounds__(128)
+    incidence_order_kernel(int64_t n, const int64_t* __restrict__ ptr, const uint32_t* __restrict__ jcount,
+                           uint32_t* __restrict__ list, uint32_t* __restrict__ epos) {
+  const int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (b >= n) return;
+  const int k = static_cast<int>(jcount[b]);
+  uint32_t* a = list + ptr[b];
+  if (k <= 24) {
+    for (int x = 1; x < k; ++x) {
+      const uint32_t v = a[x];
+      int y = x - 1;
+      while (y >= 0 && a[y] > v) {
+        a[y + 1] = a[y];
+        --y;
+      }
+      a[y + 1] = v;
+    }
+  } else {
+    auto sift = [&](int root, int end) {
+      for (;;) {
+        int child = 2 * root + 1;
+        if (child > end) break;
+        if (child + 1 <= end && a[child] < a[child + 1]) ++child;
+        if (a[root] >= a[child]) break;
+        const uint32_t t = a[root];
+        a[root] = a[child], a[child] = t;
+        root = child;
+      }
+    };
+    for (int start = (k - 2) / 2; start >= 0; --start) sift(start, k - 1);
+    for (int end = k - 1; end > 0; --end) {
+      const uint32_t t = a[0];
+      a[0] = a[end], a[end] = t;
+      sift(0, end - 1);
+    }
+  }
+  const int64_t base = ptr[b];
+  for (int x = 0; x < k; ++x) epos[a[x]] = static_cast<uint32_t>(base + x);
+}
+
+}  // namespace
+
+int build_incidence_sorted(cudaStream_t st, int64_t n, int64_t npairs, const int32_t* pairs, const int64_t* rowptr,
+                           Incidence* inc) {
+  const int64_t m = 2 * npairs;
+  MB200_TRY(inc->ptr.alloc(n + 1, st));
+  MB200_TRY(inc->list.alloc(m > 0 ? m : 1, st));
+  MB200_TRY(inc->epos.alloc(m > 0 ? m : 1, st));
+  MB200_TRY(inc->bad.alloc(1, st));
+  MB200_CUDA(cudaMemsetAsync(inc->bad.p, 0, sizeof(int32_t), st));
+  Scratch<uint32_t> jc, deg;  // jc: [0, n) second-body counts, [n, 2n) fill counters
+  const size_t nn = static_cast<size_t>(n > 0 ? n : 1);
+  MB200_TRY(jc.alloc(2 * nn, st));
+  MB200_TRY(deg.alloc(nn, st));
+  MB200_CUDA(cudaMemsetAsync(jc.p, 0, 2 * nn * sizeof(uint32_t), st));
+  const int2* p2 = reinterpret_cast<const int2*>(pairs);
+  if (npairs > 0) {
+    second_counts_kernel<<<grid_for(npairs, 256), 256, 0, st>>>(npairs, p2, jc.p);
+    MB200_LAUNCHED();
+  }
+  if (n > 0) {
+    degree_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, rowptr, jc.p, deg.p);
+    MB200_LAUNCHED();
+  } else {
+    MB200_CUDA(cudaMemsetAsync(deg.p, 0, sizeof(uint32_t), st));
+  }
+  MB200_TRY(exclusive_scan_u32_to_i64(st, n, deg.p, inc->ptr.p));
+  if (npairs > 0) {
+    incidence_fill_kernel<<<grid_for(npairs, 256), 256, 0, st>>>(npairs, p2, rowptr, inc->ptr.p, jc.p, jc.p + nn,
+                                                                inc->list.p, inc->epos.p);
+    MB200_LAUNCHED();
+    incidence_order_kernel<<<grid_for(n, 128), 128, 0, st>>>(n, inc->ptr.p, jc.p, inc->list.p, inc->epos.p);
+    MB200_LAUNCHED();
+  }
+  return MB200_OK;
+}
+
 // For the entry points that take the caller's pair list: synchronises and fails if an index was out of range.
 int check_incidence(cudaStream_t st, const Incidence& inc) {
   int32_t bad = 0;
