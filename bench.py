@@ -453,18 +453,32 @@ def run_b200(args):
                "euler": 160.0 * nloc,
                "lcp_rate": 88.0 * C + 64.0 * nloc,   # state 16 r + 16 w, {n, phi0} 32, sigma 16, ids 8; velocity records once
                "lcp_body": 32.0 * C + 176.0 * nloc}  # 8(d) iteration bytes minus the rate pass's
+        # The solver enqueues iterations ahead of the convergence test; launches queued behind the converged one return
+        # at once. They are in `calls` and in the sampled regions, so a plain average over the regions would be
+        # diluted by them: the sampled time is attributed to the launches that did work (iterations + the initial
+        # pass [+ the final body pass] of every solve), which charges the no-op launches' few microseconds to them.
+        iters_total = sum(x[0] for x in tlog)
+        executed = {"lcp_body": iters_total + 2 * len(tlog), "lcp_rate": iters_total + len(tlog)}
+        per_launch_ms = {}
         for name, (tot_ms, cnt) in stages.items():
-            stage_out[name] = {"ms_total": round(tot_ms, 4), "regions": cnt, "calls": stage_calls.get(name, cnt)}
+            calls_n = stage_calls.get(name, cnt)
+            stage_out[name] = {"ms_total": round(tot_ms, 4), "regions": cnt, "calls": calls_n}
             if name in alg and cnt > 0:
-                gbs = alg[name] / (tot_ms / cnt * 1e-3) / 1e9
-                stage_out[name].update({"avg_us": round(1e3 * tot_ms / cnt, 2), "alg_bytes": alg[name],
+                avg_ms = tot_ms / cnt
+                if name in executed and 0 < executed[name] <= calls_n:
+                    stage_out[name].update({"executed": executed[name], "noop_launches": calls_n - executed[name],
+                                            "avg_us_all_launches": round(1e3 * avg_ms, 2)})
+                    avg_ms = avg_ms * calls_n / executed[name]
+                per_launch_ms[name] = avg_ms
+                gbs = alg[name] / (avg_ms * 1e-3) / 1e9
+                stage_out[name].update({"avg_us": round(1e3 * avg_ms, 2), "alg_bytes": alg[name],
                                         "gbs": round(gbs, 1), "frac": round(gbs / peak, 4)})
         if stages["lcp_rate"][1] > 0 and stages["lcp_body"][1] > 0:
             # one operator application = one body pass + one rate pass: the dominant kernel group of the step
-            it_ms = sum(stages[k][0] / stages[k][1] for k in ("lcp_rate", "lcp_body"))
+            it_ms = per_launch_ms["lcp_rate"] + per_launch_ms["lcp_body"]
             it_bytes = 120.0 * C + 240.0 * nloc
             achieved = it_bytes / (it_ms * 1e-3) / 1e9
-            calls = stage_calls.get("lcp_rate", 0)
+            calls = executed["lcp_rate"]
             traffic = None  # DRAM bytes per iteration (body + rate) from the committed ncu capture of this workload
             try:
                 if n == 1_000_000 and args.filter == "shape":
@@ -478,9 +492,11 @@ def run_b200(args):
                         "peak_source": peak_src, "launches": 2 * calls,
                         "launches_timed": stages["lcp_rate"][1] + stages["lcp_body"][1], "avg_us": 1e3 * it_ms,
                         "share_of_step": it_ms * calls / ms,
-                        "body_pass_us": 1e3 * stages["lcp_body"][0] / stages["lcp_body"][1],
-                        "rate_pass_us": 1e3 * stages["lcp_rate"][0] / stages["lcp_rate"][1],
-                        "timing": f"CUDA events around every {max(1, args.stage_sample)}-th launch inside the timed region"}
+                        "body_pass_us": 1e3 * per_launch_ms["lcp_body"],
+                        "rate_pass_us": 1e3 * per_launch_ms["lcp_rate"],
+                        "timing": f"CUDA events around every {max(1, args.stage_sample)}-th launch inside the timed region; "
+                                  "sampled time attributed to the launches that did work (no-op launches queued behind "
+                                  "the converged iteration excluded from the count)"}
 
     cpu = None
     if not args.no_cpu_baseline:

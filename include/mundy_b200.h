@@ -511,6 +511,32 @@ int mb200_collision_step_dist(mb200_neighbor_links* links, mb200_comm* comm, mb2
 /* Bodies (owned + ghosts) and ghosts alone in the last distributed build of this rank. */
 int mb200_dist_local_counts(const mb200_neighbor_links* links, int64_t* n_local_h, int64_t* n_ghost_rows_h);
 
+/* Re-partitioning of the ranks' owned blocks on the device (splitters + all-to-all-v of the migrating bodies).
+ * The reference re-balances with stk::balance::balanceStkMesh (RCB; scrap/UnitTestMundy.cpp:1448, third party) and
+ * migrates entities through STK; here: 30-bit keys = position of the centre along the reference's Hilbert curve
+ * (math::hilbert_3d, mundy/math/src/mundy_math/Hilbert.hpp:48-85) on a 2^10 lattice over the global bounding box, a
+ * histogram of the keys' top 18 bits summed over the ranks, W - 1 splitters at the bucket boundaries nearest to equal
+ * counts, NCCL send / receive of the bodies to the rank whose key range holds them. Collective; synchronises.
+ *   owned_in        the bodies this rank owns now (n >= 0)
+ *   extra_in/out    optional per-body payload of extra_dim doubles (external forces, ...) that travels with the bodies
+ *   capacity        bodies the output arrays can hold; more arriving -> MB200_ERR_CAPACITY on this rank (owned_out->n is
+ *                   still set; every collective of the call has completed, the other ranks are not left waiting)
+ *   owned_out       the caller's OUTPUT arrays (written through the struct's pointers, the const members included;
+ *                   quat / length / kind may be NULL for spheres); owned_out->n = bodies this rank owns afterwards,
+ *                   in ascending key order (ties: by source rank, then the source's order)
+ *   origin_out      optional [capacity]: (source rank << 32) | index in that rank's owned_in
+ *   keys_out        optional [capacity]: the bodies' keys
+ *   links           optional: the rank's link handle is marked for a rebuild at its next distributed step
+ * Bodies of one bucket (16^3 lattice cells) stay together, so blocks are equal up to one bucket's population. */
+int mb200_dist_repartition(mb200_comm* comm, mb200_stream stream, mb200_neighbor_links* links,
+                           const mb200_bodies* owned_in, const double* extra_in, int extra_dim, int64_t capacity,
+                           mb200_bodies* owned_out, double* extra_out, int64_t* origin_out, uint32_t* keys_out);
+/* The keys alone: keys_out[k] = position of cell min(trunc((c_k - lo) / span * 2^10), 2^10 - 1) (per axis) along
+ * math::hilbert_3d's curve (Hilbert.hpp:48-85; visiting order pinned against UnitTestHilbert.cpp's goldens in
+ * tests/test_dist_cpu.py through mundy_b200/dist.py). lo_h: HOST double[3]. */
+int mb200_hilbert_keys(mb200_stream stream, int64_t n, const double* center, const double* lo_h, double span,
+                       uint32_t* keys_out);
+
 /* Total kernels launched by this library in the calling process (a monotone counter; for bench accounting). */
 int64_t mb200_kernel_launch_count(void);
 

@@ -113,6 +113,8 @@ SIGNATURES = {
     "mb200_search_pairs_periodic": (C.c_int, [vp, c_i64, vp, vp, P(c_dbl), vp, c_i64, P(c_i64)]),
     "mb200_narrow_phase_periodic": (C.c_int, [vp, P(Bodies), c_i64, vp, P(c_dbl), vp, vp, vp, vp]),
     "mb200_narrow_phase_no_alloc": (C.c_int, [vp, P(Bodies), c_i64, vp, vp, vp, vp, vp]),
+    "mb200_dist_repartition": (C.c_int, [vp, vp, vp, P(Bodies), vp, C.c_int, c_i64, P(Bodies), vp, vp, vp]),
+    "mb200_hilbert_keys": (C.c_int, [vp, c_i64, vp, P(c_dbl), c_dbl, vp]),
     "mb200_periodic_sep": (C.c_int, [vp, c_i64, P(c_dbl), vp, vp, vp]),
     "mb200_periodic_wrap": (C.c_int, [vp, c_i64, P(c_dbl), vp, vp]),
     "mb200_periodic_unwrap_points": (C.c_int, [vp, c_i64, P(c_dbl), vp, vp, vp]),

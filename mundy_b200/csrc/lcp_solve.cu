@@ -458,7 +458,8 @@ __global__ void __launch_bounds__(kBodyThreads)
       if (SIX && W) st3(W, b, w);
     }
   }
-  if (halo && blockIdx.x < nb_ctas) {
+  if constexpr (halo) {
+  if (blockIdx.x < nb_ctas) {
     // the boundary CTAs' remote stores are ordered before the flag the last of them publishes to all ranks (release,
     // system scope); the consumers are the peers' rate_pass_kernels
     // (bar.sync orders the CTA's stores before thread 0's system-scope fence: the grid-sync pattern, one fence per CTA)
@@ -474,9 +475,10 @@ __global__ void __launch_bounds__(kBodyThreads)
       __threadfence_system();
       st_relaxed_sys(&a.peer->ctrl[t]->halo_flag[a.peer->me], a.halo_seq);
     }
-  } else if (halo && nb_ctas == 0 && blockIdx.x == 0) {
+  } else if (nb_ctas == 0 && blockIdx.x == 0) {
     // nothing of this rank is ghosted anywhere: the peers still wait for its flag
     if (t < a.peer->world && t != a.peer->me) st_relaxed_sys(&a.peer->ctrl[t]->halo_flag[a.peer->me], a.halo_seq);
+  }
   }
   if (FINAL) {
     const double m = block_max(speed, sh, 0.0);

@@ -232,3 +232,96 @@ def local_counts(links):
     a, b = C.c_int64(0), C.c_int64(0)
     check(lib.mb200_dist_local_counts(links._h, C.byref(a), C.byref(b)), "dist_local_counts")
     return a.value, b.value
+
+
+# ---- re-partitioning (csrc/repartition.cu) ------------------------------------------------------------------------------
+HILBERT_BITS = 10       # lattice cells per axis of the repartitioning keys
+BUCKET_SHIFT = 12       # keys >> 12: the 2^18 histogram buckets the splitters are chosen among
+
+
+def lattice_of(centers):
+    """(lo, span) of the repartitioning lattice: the bounding box of ALL ranks' centres (list of (n_r, 3) arrays)."""
+    pts = [np.asarray(c, dtype=np.float64) for c in centers if len(c)]
+    if not pts:
+        return np.zeros(3), 1.0
+    lo = np.min([p.min(axis=0) for p in pts], axis=0)
+    hi = np.max([p.max(axis=0) for p in pts], axis=0)
+    span = float(np.max(hi - lo))
+    return lo, (span if span > 0 else 1.0)
+
+
+def hilbert_keys(center, lo, span, bits=HILBERT_BITS):
+    """numpy statement of mb200_hilbert_keys: the reference curve's index of every centre's lattice cell."""
+    center = np.asarray(center, dtype=np.float64).reshape(-1, 3)
+    cells = np.clip(((center - lo) / span * (1 << bits)).astype(np.int64), 0, (1 << bits) - 1)
+    return hilbert_index_reference(cells, bits).astype(np.uint32)
+
+
+def repartition_plan(keys_per_rank):
+    """numpy statement of mb200_dist_repartition's decisions. keys_per_rank: list (one entry per rank) of uint32 key arrays
+    in the ranks' owned order. Returns (split, dest): split[r] = first bucket of rank r (split[W] = 2^18), and per rank
+    the list `dest[r]` of (source rank, source index) pairs it owns afterwards, in its final order (ascending key; ties by
+    source rank, then source order)."""
+    W = len(keys_per_rank)
+    nb = 1 << (3 * HILBERT_BITS - BUCKET_SHIFT)
+    hist = np.zeros(nb, dtype=np.int64)
+    for k in keys_per_rank:
+        hist += np.bincount(np.asarray(k, dtype=np.int64) >> BUCKET_SHIFT, minlength=nb)
+    total = int(hist.sum())
+    below = np.concatenate([[0], np.cumsum(hist)])          # below[b] = bodies in buckets < b
+    split = [0] * (W + 1)
+    for r in range(1, W):
+        split[r] = int(np.searchsorted(below, (total * r) // W, side="left"))  # first b with below[b] >= r N / W
+    split[W] = nb
+    dest = []
+    for r in range(W):
+        rows = []
+        for src, k in enumerate(keys_per_rank):
+            k = np.asarray(k, dtype=np.int64)
+            sel = np.nonzero(((k >> BUCKET_SHIFT) >= split[r]) & ((k >> BUCKET_SHIFT) < split[r + 1]))[0]
+            sel = sel[np.argsort(k[sel], kind="stable")]
+            rows.append(np.stack([np.full(len(sel), src, dtype=np.int64), sel.astype(np.int64), k[sel]], axis=1))
+        allr = np.concatenate(rows) if rows else np.zeros((0, 3), dtype=np.int64)
+        allr = allr[np.argsort(allr[:, 2], kind="stable")]
+        dest.append(allr[:, :2])
+    return split, dest
+
+
+def device_hilbert_keys(center, lo, span):
+    import torch
+    from .ops import _f64, _stream
+    n = center.shape[0]
+    keys = torch.empty(n, dtype=torch.int32, device=center.device)
+    lo_h = (C.c_double * 3)(*[float(x) for x in lo])
+    check(lib.mb200_hilbert_keys(_stream(), n, _f64(center), lo_h, float(span), C.c_void_p(keys.data_ptr())),
+          "hilbert_keys")
+    return keys
+
+
+def repartition(comm, center, radius, quat=None, length=None, kind=None, extra=None, capacity=None, links=None):
+    """Collective. Tensors of the bodies THIS RANK owns -> dict of the tensors it owns afterwards (views of
+    capacity-sized buffers cut to the new count), plus 'origin' ((source rank << 32) | source index) and 'keys'."""
+    import torch
+    from .ops import _f64, _i32, _stream, make_bodies
+    n = radius.numel()
+    cap = int(capacity) if capacity is not None else max(2 * n, 1024)
+    dev = radius.device
+    out = {"center": torch.empty((cap, 3), dtype=torch.float64, device=dev),
+           "radius": torch.empty(cap, dtype=torch.float64, device=dev),
+           "quat": torch.empty((cap, 4), dtype=torch.float64, device=dev) if quat is not None else None,
+           "length": torch.empty(cap, dtype=torch.float64, device=dev) if length is not None else None,
+           "kind": torch.empty(cap, dtype=torch.int32, device=dev) if kind is not None else None}
+    edim = 0 if extra is None else int(extra.shape[1])
+    extra_out = torch.empty((cap, edim), dtype=torch.float64, device=dev) if edim else None
+    origin = torch.empty(cap, dtype=torch.int64, device=dev)
+    keys = torch.empty(cap, dtype=torch.int32, device=dev)
+    b_in = make_bodies(center, radius, quat, length, kind)
+    b_out = make_bodies(out["center"], out["radius"], out["quat"], out["length"], out["kind"])
+    check(lib.mb200_dist_repartition(comm._h, _stream(), links._h if links is not None else None, C.byref(b_in),
+                                     _f64(extra), edim, cap, C.byref(b_out), _f64(extra_out),
+                                     C.c_void_p(origin.data_ptr()), C.c_void_p(keys.data_ptr())), "dist_repartition")
+    m = int(b_out.n)
+    res = {k: (v[:m] if v is not None else None) for k, v in out.items()}
+    res["extra"] = extra_out[:m] if extra_out is not None else None
+    res["origin"], res["keys"] = origin[:m], keys[:m]
+    return res

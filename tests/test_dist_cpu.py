@@ -114,3 +114,87 @@ def test_comm_abi_without_device():
         buf = C.create_string_buffer(128)
         st = _capi.lib.mb200_comm_create(C.byref(h), 1, 0, buf)
         assert st == -2  # MB200_ERR_CUDA: no device, no CPU fallback
+
+
+# ---- re-partitioning: the numpy statement of csrc/repartition.cu's decisions --------------------------------------------
+def test_repartition_keys_order_bodies_like_hilbert_order():
+    rng = np.random.default_rng(1)
+    c = rng.uniform(-3.0, 40.0, (20000, 3))
+    lo, span = mbd.lattice_of([c[:7000], c[7000:]])
+    keys = mbd.hilbert_keys(c, lo, span)
+    assert keys.max() < (1 << 30)
+    assert np.array_equal(np.argsort(keys, kind="stable"), mbd.hilbert_order(c))
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_repartition_plan_properties(world):
+    rng = np.random.default_rng(world)
+    n = 30000
+    c = rng.uniform(0.0, 60.0, (n, 3))
+    owner = rng.choice(world, size=n, p=np.arange(1, world + 1) / np.arange(1, world + 1).sum())
+    per = [np.nonzero(owner == r)[0] for r in range(world)]
+    lo, span = mbd.lattice_of([c[ix] for ix in per])
+    keys = [mbd.hilbert_keys(c[ix], lo, span) for ix in per]
+    split, dest = mbd.repartition_plan(keys)
+    assert split[0] == 0 and split[-1] == 1 << 18 and all(a <= b for a, b in zip(split, split[1:]))
+    gid = [np.array([per[s][i] for s, i in d], dtype=np.int64) for d in dest]
+    assert sorted(np.concatenate(gid).tolist()) == list(range(n))          # every body has exactly one new owner
+    allk = np.concatenate([mbd.hilbert_keys(c[g], lo, span).astype(np.int64) for g in gid])
+    assert np.all(np.diff(allk) >= 0)                                        # rank order = curve order, sorted inside
+    biggest = np.bincount(np.concatenate(keys).astype(np.int64) >> mbd.BUCKET_SHIFT).max()
+    sizes = [len(g) for g in gid]
+    assert max(sizes) - min(sizes) <= 2 * biggest                            # equal up to one bucket's population
+    # bodies of one bucket stay together
+    for r, g in enumerate(gid):
+        b = mbd.hilbert_keys(c[g], lo, span).astype(np.int64) >> mbd.BUCKET_SHIFT
+        assert len(g) == 0 or (b.min() >= split[r] and b.max() < split[r + 1])
+
+
+def _splitter_worker(rank, world, port, out):
+    """What every rank does with the all-reduced histogram must give the splitters of the global statement."""
+    try:
+        os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        rng = np.random.default_rng(11)
+        n = 20000
+        c = rng.uniform(0.0, 30.0, (n, 3))
+        owner = rng.integers(0, world, n)
+        per = [np.nonzero(owner == r)[0] for r in range(world)]
+        # bounding boxes all-gathered (6 doubles per rank), as the device code does
+        mine = c[per[rank]]
+        box = torch.tensor(np.concatenate([mine.min(axis=0), mine.max(axis=0)]))
+        boxes = [torch.zeros(6, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(boxes, box)
+        lo = np.min([b[:3].numpy() for b in boxes], axis=0)
+        span = float(np.max(np.max([b[3:].numpy() for b in boxes], axis=0) - lo))
+        lo_g, span_g = mbd.lattice_of([c[ix] for ix in per])
+        assert np.array_equal(lo, lo_g) and span == span_g
+        keys = mbd.hilbert_keys(mine, lo, span).astype(np.int64)
+        hist = torch.tensor(np.bincount(keys >> mbd.BUCKET_SHIFT, minlength=1 << 18))
+        dist.all_reduce(hist)
+        below = np.concatenate([[0], np.cumsum(hist.numpy())])
+        split = [0] + [int(np.searchsorted(below, (n * r) // world, side="left")) for r in range(1, world)] + [1 << 18]
+        want_split, dest = mbd.repartition_plan([mbd.hilbert_keys(c[ix], lo, span) for ix in per])
+        assert split == want_split
+        # send counts of this rank = what the destination ranks expect from it
+        bucket = keys >> mbd.BUCKET_SHIFT
+        send = [int(np.sum((bucket >= split[r]) & (bucket < split[r + 1]))) for r in range(world)]
+        assert send == [int(np.sum(d[:, 0] == rank)) for d in dest]
+        out.put((rank, "ok"))
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        out.put((rank, f"{type(e).__name__}: {e}"))
+
+
+def test_repartition_splitters_agree_across_gloo_ranks():
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_splitter_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [out.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res

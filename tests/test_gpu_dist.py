@@ -152,3 +152,133 @@ def test_multi_gpu_step_matches_single_gpu(cuda, world, exchange):
         p.join(timeout=60)
     assert all(r[1] == "ok" for r in res), res
     print(f"world {world} {exchange}:", sorted(res)[0][2])
+
+
+# ---- re-partitioning on the device (mb200_dist_repartition) -------------------------------------------------------------
+def _scrambled(world, n=6000, seed=5):
+    """A rod workload in generation order (not curve order) and an uneven random assignment of its bodies to the ranks."""
+    w = wl.rods(n, phi=0.1)
+    rng = np.random.default_rng(seed)
+    p = np.arange(1, world + 1, dtype=np.float64)
+    owner = rng.choice(world, size=n, p=p / p.sum())
+    return w, owner
+
+
+def _repartition_case(comm, rank, world, dev):
+    """Repartitions a scrambled assignment; checks every decision against the numpy statement (dist.repartition_plan) and
+    the travelling payload; returns (this rank's new tensors, the global set in the new global order)."""
+    from mundy_b200 import dist as mbd
+    w, owner = _scrambled(world)
+    n = len(owner)
+    mine = np.nonzero(owner == rank)[0]
+    per_rank = [np.nonzero(owner == r)[0] for r in range(world)]
+    extra = np.concatenate([np.arange(n, dtype=np.float64)[:, None], w["center"] * 0.5 + 1.0], axis=1)  # id + a payload
+    res = mbd.repartition(comm, _dev(w["center"][mine], dev), _dev(w["radius"][mine], dev), _dev(w["quat"][mine], dev),
+                          _dev(w["length"][mine], dev), _dev(w["kind"][mine], dev, torch.int32),
+                          extra=_dev(extra[mine], dev), capacity=n)
+    lo, span = mbd.lattice_of([w["center"][ix] for ix in per_rank])
+    keys = [mbd.hilbert_keys(w["center"][ix], lo, span) for ix in per_rank]
+    split, dest = mbd.repartition_plan(keys)
+    want = dest[rank]                                    # (source rank, source index) in this rank's final order
+    gid = np.array([per_rank[s][i] for s, i in want], dtype=np.int64)
+    assert res["radius"].numel() == len(want)
+    assert np.array_equal(res["origin"].cpu().numpy(), (want[:, 0] << 32) | want[:, 1])
+    assert np.array_equal(res["extra"].cpu().numpy()[:, 0].astype(np.int64), gid)
+    assert np.array_equal(res["extra"].cpu().numpy(), extra[gid])
+    for name in ("center", "quat", "radius", "length", "kind"):
+        assert np.array_equal(res[name].cpu().numpy(), w[name][gid]), name
+    k = res["keys"].cpu().numpy().astype(np.int64)
+    assert np.all(np.diff(k) >= 0)
+    assert np.array_equal(k, np.concatenate([keys[s][[i]] for s, i in want]).astype(np.int64) if len(want) else k)
+    # blocks are equal up to one bucket's population
+    sizes = [len(d) for d in dest]
+    biggest = max(np.bincount(np.concatenate(keys).astype(np.int64) >> mbd.BUCKET_SHIFT))
+    assert max(sizes) - min(sizes) <= 2 * biggest, (sizes, biggest)
+    order = np.concatenate([[per_rank[s][i] for s, i in d] for d in dest]).astype(np.int64)  # new global order
+    return res, w, order, sizes
+
+
+def _steps_after_repartition(res, w, order, sizes, rank, comm, dev):
+    """The distributed step on the repartitioned blocks against the single-GPU step on the same bodies in the new order."""
+    from mundy_b200 import dist as mbd
+    from mundy_b200 import ops
+    wg = {k: (v[order] if isinstance(v, np.ndarray) and v.shape[:1] == (len(order),) else v) for k, v in w.items()}
+    o0 = int(np.sum(sizes[:rank]))
+    outs = []
+    for which in ("single", "dist"):
+        if which == "single":
+            b, c, q = _bodies(wg, dev)
+        else:
+            c, q = res["center"].clone(), res["quat"].clone()
+            b = ops.make_bodies(c, res["radius"], q, res["length"], res["kind"])
+        links = ops.NeighborLinks().set_search_buffer(BUF).set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
+        F = torch.zeros((c.shape[0], 3), dtype=torch.float64, device=dev)
+        hist = []
+        for _ in range(2):
+            F.zero_()
+            ops.abc_flow_force(c, F)
+            if which == "single":
+                st = links.step(b, MU, DT, TOL, 10000, fixed_iters=8, F_ext=F)
+            else:
+                st = mbd.step_dist(links, comm, b, MU, DT, TOL, 10000, fixed_iters=8, F_ext=F)
+            hist.append((c.cpu().numpy().copy(), q.cpu().numpy().copy(), st.lcp.max_abs_projected_sep))
+        outs.append(hist)
+    for x, y in zip(*outs):
+        n_own = y[0].shape[0]
+        assert _rel(y[0], x[0][o0:o0 + n_own]) <= 1e-12
+        assert np.max(np.abs(y[1] - x[1][o0:o0 + n_own])) <= 1e-12
+        assert abs(y[2] - x[2]) <= 1e-9 * abs(x[2])
+
+
+def test_world1_repartition_sorts_along_the_reference_curve(cuda):
+    from mundy_b200 import dist as mbd
+    comm = mbd.Comm()
+    res, w, order, sizes = _repartition_case(comm, 0, 1, "cuda:0")
+    assert sizes == [len(order)]
+    # one rank: the new order is the stable sort along the curve, i.e. dist.hilbert_order
+    assert np.array_equal(order, mbd.hilbert_order(w["center"]))
+    _steps_after_repartition(res, w, order, sizes, 0, comm, "cuda:0")
+
+
+def _repart_worker(rank, world, port, out):
+    try:
+        import torch.distributed as dist
+        from mundy_b200 import dist as mbd
+        os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        dev = f"cuda:{rank}"
+        comm = mbd.Comm()
+        res, w, order, sizes = _repartition_case(comm, rank, world, dev)
+        _steps_after_repartition(res, w, order, sizes, rank, comm, dev)
+        # a rank whose arrays are too small reports it without leaving the others waiting
+        from mundy_b200._capi import Mb200Error
+        mine = np.nonzero(_scrambled(world)[1] == rank)[0]
+        try:
+            mbd.repartition(comm, _dev(w["center"][mine], dev), _dev(w["radius"][mine], dev), capacity=8 if rank == 0 else 6000)
+            failed = False
+        except Mb200Error as e:
+            failed = "capacity" in str(e)
+        assert failed == (rank == 0)
+        out.put((rank, "ok", sizes))
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        out.put((rank, f"{type(e).__name__}: {e}\n{traceback.format_exc()}", None))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_multi_gpu_repartition(cuda, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run with gpurun --gpus {world})")
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_repart_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [out.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res
+    print(f"world {world} repartition: block sizes", sorted(res)[0][2])

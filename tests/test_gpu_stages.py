@@ -164,8 +164,68 @@ def test_links_coo_to_crs(cuda, n, m, empty):
     assert np.array_equal(linked[host(links), host(slots)], ent)
 
 
+def test_links_coo_to_crs_reference_unit_test_case(cuda):
+    """The reference's own check of the synchroniser, restated for pair links
+    (mundy/mesh/tests/unit_tests/UnitTestNgpLinkData.cpp): links are declared on freshly made entities
+    (initialize_links :115-129, declare_and_validate_relations :131-160), the expected CRS connectivity is the
+    inversion of that initialisation data and is compared per entity AS A SET (validate_crs_connectivity :276-327);
+    then the relations of every link are destroyed and re-declared in swapped slots on the device
+    (modify_ngp_link_data :241-273), which must leave the sets unchanged; a destroyed relation (empty slot,
+    NgpCOOToCRSSynchronizer.hpp:449) drops out of its entity's row and of the atomic counts (:405-468)."""
+    from mundy_b200 import ops
+    n_links = 37
+    # link k on the new entities (2k, 2k + 1), as initialize_links makes them; some entities get further links so that
+    # rows hold more than one link (the reference's sets can)
+    init = [[2 * k, 2 * k + 1] for k in range(n_links)]
+    extra = [[0, 5], [5, 9], [9, 0], [73, 1]]
+    link_and_linked = init + extra
+    n_ent = 2 * n_links
+
+    def expected(lk):  # validate_crs_connectivity :283-290
+        conn = {}
+        for link, ents in enumerate(lk):
+            for e in ents:
+                if e >= 0:
+                    conn.setdefault(e, set()).add(link)
+        return conn
+
+    def check(lk):
+        off, links, slots = (host(t) for t in ops.links_coo_to_crs(n_ent, dev(np.array(lk), torch.int32)))
+        exp = expected(lk)
+        for e in range(n_ent):
+            row = links[off[e]:off[e + 1]]
+            assert set(row.tolist()) == exp.get(e, set())
+            assert len(row) == sum(1 for ents in lk for x in ents if x == e)  # the count of gather_part_1_count
+            for l, sl in zip(row, slots[off[e]:off[e + 1]]):
+                assert lk[l][sl] == e
+        return off
+
+    check(link_and_linked)
+    swapped = [[b, a] for a, b in link_and_linked]  # modify_ngp_link_data: destroy both, declare in the other order
+    check(swapped)
+    destroyed = [list(x) for x in swapped]
+    destroyed[3][0] = -1   # destroy_relation without a new declaration: an empty slot
+    destroyed[38][1] = -1
+    off = check(destroyed)
+    assert off[-1] == 2 * len(link_and_linked) - 2
+
+
 def test_links_coo_to_crs_rejects_out_of_range(cuda):
     from mundy_b200 import ops
     from mundy_b200._capi import Mb200Error
     with pytest.raises(Mb200Error):
         ops.links_coo_to_crs(4, dev(np.array([[0, 4]]), torch.int32))
+
+
+@pytest.mark.parametrize("n", [0, 1, 257, 50_000])
+def test_hilbert_keys_match_the_reference_curve(cuda, n):
+    """mb200_hilbert_keys against dist.hilbert_index_reference (pinned to math::hilbert_3d's visiting order and the
+    goldens of UnitTestHilbert.cpp in tests/test_dist_cpu.py): integer work, exact."""
+    from mundy_b200 import dist as mbd
+    rng = np.random.default_rng(n + 3)
+    c = rng.uniform(-7.0, 31.0, (n, 3))
+    if n > 1:
+        c[0], c[1] = c.min(axis=0), c.max(axis=0)  # both corners of the lattice
+    lo, span = mbd.lattice_of([c])
+    got = host(mbd.device_hilbert_keys(dev(c), lo, span)).astype(np.int64)
+    assert np.array_equal(got, mbd.hilbert_keys(c, lo, span).astype(np.int64))
