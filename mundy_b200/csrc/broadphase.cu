@@ -772,8 +772,10 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   search_spheres_kernel<<<bgrid, 256, 0, st>>>(n, b->center, b->radius, b->length, b->kind, explicit_S, h->buffer,
                                                sr.p, partials.p);
   MB200_LAUNCHED();
-  std::vector<double> hp(7 * static_cast<size_t>(bgrid));
-  MB200_CUDA(cudaMemcpyAsync(hp.data(), partials.p, hp.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  const size_t hp_count = 7 * static_cast<size_t>(bgrid);
+  double* hp = static_cast<double*>(pinned_scratch(hp_count * sizeof(double)));
+  if (!hp) return MB200_ERR_CUDA;
+  MB200_CUDA(cudaMemcpyAsync(hp, partials.p, hp_count * sizeof(double), cudaMemcpyDeviceToHost, st));
   MB200_CUDA(cudaStreamSynchronize(st));
   GridParams gp;
   double lo[3] = {hp[0], hp[1], hp[2]}, hi[3] = {hp[3], hp[4], hp[5]}, smax = hp[6];
@@ -898,9 +900,11 @@ int build_links(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies* b,
   launch_find(std::false_type{}, nullptr, nullptr);
   MB200_LAUNCHED();
   MB200_TRY(exclusive_scan_u32_to_i64(st, n, counts.p, rowptr.p));
-  int64_t total = 0;
-  MB200_CUDA(cudaMemcpyAsync(&total, rowptr.p + n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  int64_t* total_h = static_cast<int64_t*>(pinned_scratch(sizeof(int64_t)));
+  if (!total_h) return MB200_ERR_CUDA;
+  MB200_CUDA(cudaMemcpyAsync(total_h, rowptr.p + n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   MB200_CUDA(cudaStreamSynchronize(st));
+  const int64_t total = *total_h;
   if (total >= (int64_t(1) << 30)) {
     set_error("pair list exceeds 2^30 entries");
     return MB200_ERR_CAPACITY;
@@ -941,10 +945,11 @@ int links_generate(cudaStream_t st, mb200_neighbor_links* h, const mb200_bodies*
                                                      shape ? h->ref_b1.p : nullptr, 0.5 * h->buffer, h->flag.p,
                                                    h->periodic);
     MB200_LAUNCHED();
-    int32_t moved = 0;
-    MB200_CUDA(cudaMemcpyAsync(&moved, h->flag.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    int32_t* moved = static_cast<int32_t*>(pinned_scratch(sizeof(int32_t)));
+    if (!moved) return MB200_ERR_CUDA;
+    MB200_CUDA(cudaMemcpyAsync(moved, h->flag.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     MB200_CUDA(cudaStreamSynchronize(st));
-    rebuild = moved != 0;
+    rebuild = *moved != 0;
   }
   if (rebuild) {
     StageScope ps(MB200_STAGE_BROADPHASE, st);

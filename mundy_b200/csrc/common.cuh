@@ -81,6 +81,11 @@ struct StageScope {
 // Verifies that a device exists before the first compute call (no CPU fallback).
 int require_device();
 
+// Page-locked host scratch of the calling thread (grows, kept until the thread ends; nullptr if it cannot be had): the
+// landing place of the small device -> host reads a step waits on. A copy into pageable memory is staged by the driver
+// and costs tens of microseconds more per read.
+void* pinned_scratch(size_t bytes);
+
 // Stream-ordered scratch buffer (cudaMallocAsync pool; freed on the same stream when it goes out of scope).
 template <typename T>
 struct Scratch {

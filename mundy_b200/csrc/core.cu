@@ -90,6 +90,33 @@ std::atomic<long long> g_launches{0};
 
 void set_error(const std::string& msg) { t_error = msg; }
 
+namespace {
+struct PinnedScratch {
+  void* p = nullptr;
+  size_t cap = 0;
+  ~PinnedScratch() {
+    if (p) cudaFreeHost(p);
+  }
+};
+}  // namespace
+void* pinned_scratch(size_t bytes) {
+  static thread_local PinnedScratch s;
+  if (bytes > s.cap) {
+    if (s.p) cudaFreeHost(s.p);
+    s.p = nullptr, s.cap = 0;
+    size_t want = 4096;
+    while (want < bytes) want <<= 1;
+    if (cudaHostAlloc(&s.p, want, cudaHostAllocPortable) != cudaSuccess) {
+      (void)cudaGetLastError();
+      s.p = nullptr;
+      set_error("cudaHostAlloc of " + std::to_string(want) + " bytes of page-locked host memory failed");
+      return nullptr;
+    }
+    s.cap = want;
+  }
+  return s.p;
+}
+
 int require_device() {
   static std::atomic<int> ok{0};
   if (ok.load(std::memory_order_acquire)) return MB200_OK;

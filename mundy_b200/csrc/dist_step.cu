@@ -740,10 +740,11 @@ extern "C" int mb200_collision_step_dist(mb200_neighbor_links* h, mb200_comm* co
       MB200_CUDA(cudaMemcpyAsync(D.flag_all.p, &one, sizeof(int32_t), cudaMemcpyHostToDevice, st));
     }
     MB200_NCCL(nccl->AllReduce(D.flag_all.p, D.flag_all.p + 1, 1, ncclInt32, ncclMax, comm->comm, st));
-    int32_t any = 0;
-    MB200_CUDA(cudaMemcpyAsync(&any, D.flag_all.p + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    int32_t* any = static_cast<int32_t*>(pinned_scratch(sizeof(int32_t)));
+    if (!any) return MB200_ERR_CUDA;
+    MB200_CUDA(cudaMemcpyAsync(any, D.flag_all.p + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     MB200_CUDA(cudaStreamSynchronize(st));
-    rebuild = any != 0;
+    rebuild = *any != 0;
   }
   if (rebuild) {
     StageScope ps(MB200_STAGE_BROADPHASE, st);
