@@ -498,6 +498,12 @@ def run_b200(args):
                                   "sampled time attributed to the launches that did work (no-op launches queued behind "
                                   "the converged iteration excluded from the count)"}
 
+            if roofline["frac"] > 1.0:
+                roofline["note"] = ("SURVEY 8(d)'s bytes charge every contact to every pass; the body pass visits only the "
+                                    "contacts whose activity bit is set, so with few active contacts the kernels move "
+                                    "fewer bytes than the model and the fraction exceeds 1: see stages.lcp_rate (which "
+                                    "streams every contact) for a bandwidth figure")
+
     cpu = None
     if not args.no_cpu_baseline:
         secs, info = cpu_steps(args.cpu_bodies, args.cpu_steps, 1, filt)
