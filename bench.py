@@ -283,7 +283,7 @@ def run_b200(args):
     filt = args.filter == "shape"
     dev = torch.device("cuda", local)
     comm = None
-    if world > 1:
+    if world > 1 or os.environ.get("MB200_BENCH_FORCE_DIST"):  # (the variable: the distributed code path on one GPU, a diagnostic)
         # weak scaling: world * n bodies in one box at the same density, ordered along the Hilbert curve; rank r owns the
         # r-th block of n bodies and holds ONLY that block (mundy_b200/dist.py): the library fetches the ghosts
         from mundy_b200 import dist as mbd

@@ -80,7 +80,9 @@ int peer_setup(mb200_comm* comm, cudaStream_t st, int64_t rows) {
   const int W = comm->world, me = comm->rank;
   if (P.tried && rows <= P.rows) return MB200_OK;
   const char* env = getenv("MB200_DIST_EXCHANGE");
-  const bool want = !(env && std::strcmp(env, "nccl") == 0) && W > 1 && W <= kMaxRanks;
+  // (MB200_DIST_EXCHANGE=peer also takes the peer-memory kernels with a single rank: a diagnostic of their own cost)
+  const bool want = !(env && std::strcmp(env, "nccl") == 0) && (W > 1 || (env && std::strcmp(env, "peer") == 0)) &&
+                    W <= kMaxRanks;
   if (P.tried) {
     // a larger arena is needed: every rank gets here in the same step (rows derives from the global body count);
     // peers must have closed their mappings before the memory is freed

@@ -596,10 +596,17 @@ __global__ void __launch_bounds__(256) halo_unpack_kernel(int64_t count, int rec
 }
 
 // Velocity record of a body for the rate pass. Peer mode: ghost rows are written by other GPUs over NVLink while this
-// kernel runs, so they are read with coherent loads (ld.global.nc must not see data that changes during the kernel).
+// kernel is resident, so they are read with coherent loads (ld.global.nc must not see data that changes during the
+// kernel). The loads are plain asm, free to be scheduled like any other load (a volatile asm with a memory clobber kept
+// the four gathers of a contact in program order behind each other and behind the state store: +5 us per launch); what
+// keeps them behind the halo wait is their ADDRESS: the kernel derives the base pointer it hands down here from a value
+// produced after the wait (rate_pass_kernel).
 template <bool PEER>
 __device__ inline D4 ld_vel(const D4* p) {
-  return PEER ? ld256(p) : ldg256(p);
+  if (!PEER) return ldg256(p);
+  D4 r;
+  asm("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+  return r;
 }
 
 // MODE 0: initial pass (state holds gamma_0; g_0 = D^T M D gamma_0, residual only). MODE 1: iteration pass.
@@ -610,26 +617,27 @@ __device__ inline D4 ld_vel(const D4* p) {
 // One contact of the rate pass: gamma of this iteration, g = D^T U from the gathered velocity records, the new state,
 // the contact's terms of the residual and of the three BB sums. Returns the contact's activity for the next iteration.
 template <int ARM, int MODE, bool PEER>
-__device__ inline bool rate_contact(const LcpArgs& a, int64_t c, const double2& sp, const D4& r0, const D4& r1,
-                                    const D4& r2, const double2& sg, const int2& p, double alpha, int first, double& res,
-                                    double& xx, double& xg, double& gg) {
+__device__ inline bool rate_contact(const LcpArgs& a, const D4* vel, bool counted, int64_t c,
+                                    const double2& sp, const D4& r0, const D4& r1, const D4& r2, const double2& sg,
+                                    const int2& p, double alpha, int first, double& res, double& xx, double& xg,
+                                    double& gg) {
   const V3 n{r0.x, r0.y, r0.z};
   V3 ui, uj, wi{0, 0, 0}, wj{0, 0, 0};
   const V3 ai{r1.x, r1.y, r1.z}, aj{r2.x, r2.y, r2.z};
   if (ARM != ARM_NONE) {
-    const D4 v0 = ld_vel<PEER>(a.vel + 2 * p.x), v1 = ld_vel<PEER>(a.vel + 2 * p.x + 1);
-    const D4 v2 = ld_vel<PEER>(a.vel + 2 * p.y), v3 = ld_vel<PEER>(a.vel + 2 * p.y + 1);
+    const D4 v0 = ld_vel<PEER>(vel + 2 * p.x), v1 = ld_vel<PEER>(vel + 2 * p.x + 1);
+    const D4 v2 = ld_vel<PEER>(vel + 2 * p.y), v3 = ld_vel<PEER>(vel + 2 * p.y + 1);
     ui = V3{v0.x, v0.y, v0.z}, wi = V3{v1.x, v1.y, v1.z};
     uj = V3{v2.x, v2.y, v2.z}, wj = V3{v3.x, v3.y, v3.z};
   } else {
-    const D4 v0 = ld_vel<PEER>(a.vel + p.x), v2 = ld_vel<PEER>(a.vel + p.y);
+    const D4 v0 = ld_vel<PEER>(vel + p.x), v2 = ld_vel<PEER>(vel + p.y);
     ui = V3{v0.x, v0.y, v0.z}, uj = V3{v2.x, v2.y, v2.z};
   }
   const double gam = gamma_of<MODE>(sp, r0.w, alpha, a.dt, first);
   const double g = rate_of<ARM>(n, ui, uj, wi, wj, ai, aj, sg.x, sg.y);
   a.state[c] = make_double2(gam, g);
   const double sep_new = r0.w + a.dt * g;  // KokkosLCP.cpp:500-521
-  if (!a.counted || a.counted[c]) {  // a cut contact is summed by the rank that owns its first body
+  if (counted) {  // a cut contact is summed by the rank that owns its first body
     const double v = (gam < 1e-12) ? fabs(fmin(sep_new, 0.0)) : fabs(sep_new);
     res = fmax(res, v);
     if (MODE == 1) {  // KokkosLCP.cpp:536-556
@@ -705,6 +713,14 @@ __global__ void __launch_bounds__(kRateThreads) rate_pass_kernel(LcpArgs a, int 
     }
     __syncthreads();
   }
+  // peer mode: the base of the velocity records as a value the compiler cannot know before this point (a zero it has to
+  // take from a volatile asm placed after the wait): every gather's address depends on it, none can move above the wait
+  const D4* vel = a.vel;
+  if (PEER) {
+    unsigned long long zero;
+    asm volatile("mov.u64 %0, 0;" : "=l"(zero)::"memory");
+    vel = a.vel + zero;
+  }
   for (int64_t k = 0;; ++k) {
     const int64_t tile = blockIdx.x + k * G;
     if (tile >= ntiles) break;
@@ -757,8 +773,12 @@ __global__ void __launch_bounds__(kRateThreads) rate_pass_kernel(LcpArgs a, int 
       if (ARM == ARM_AXIAL) sg = ldg128(a.sig + c);
       if (ARM == ARM_GENERAL) r1 = ldg256(a.rec + a.npairs + c), r2 = ldg256(a.rec + 2 * a.npairs + c);
     }
+    // multi-GPU: is the contact counted in this rank's sums? Requested here, with the streams, not where it is used
+    bool counted = true;
+    if (a.counted && valid) counted = __ldg(a.counted + c) != 0;
     const uint32_t old_bits = a.active[cw >> 5];  // one address per warp: a broadcast
-    const bool flag = valid && rate_contact<ARM, MODE, PEER>(a, c, sp, r0, r1, r2, sg, p, alpha, first, res, xx, xg, gg);
+    const bool flag =
+        valid && rate_contact<ARM, MODE, PEER>(a, vel, counted, c, sp, r0, r1, r2, sg, p, alpha, first, res, xx, xg, gg);
     const uint32_t bits = __ballot_sync(0xffffffffu, flag);
     if ((t & 31) == 0) a.active[cw >> 5] = bits;
     if (valid && flag != (((old_bits >> (t & 31)) & 1u) != 0)) flip_entries(a.inc_epos, a.inc_ptr, a.bmask, c, p);
