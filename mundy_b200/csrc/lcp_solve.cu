@@ -284,8 +284,10 @@ constexpr int kChunk = MB200_BODY_CHUNK;
 // against 66 us at ptxas' own 72 registers: the spills go through the same load/store path as the gathers.)
 // HALO: the peer-memory multi-GPU form (ownership classes, boundary bodies first, remote stores, early halo flag); a
 // template parameter so that the single-GPU kernel does not carry its registers (72 against 92).
+// (axial arms, peer mode: six CTAs per SM, i.e. at most 80 registers, which the single-GPU form takes anyway: the peer-mode form
+// would take 84 and lose a CTA)
 template <int ARM, int MODE, bool FINAL, bool HALO>
-__global__ void __launch_bounds__(kBodyThreads)
+__global__ void __launch_bounds__(kBodyThreads, (ARM == ARM_AXIAL && HALO) ? 6 : 0)
     body_pass_kernel(LcpArgs a, int first, double* __restrict__ F, double* __restrict__ T, double* __restrict__ U,
                      double* __restrict__ W, const double* __restrict__ U_ext, const double* __restrict__ W_ext) {
   if (!FINAL && a.state_blk->done) return;
@@ -321,9 +323,7 @@ __global__ void __launch_bounds__(kBodyThreads)
     const int64_t beg = __ldg(a.inc_ptr + b), end = __ldg(a.inc_ptr + b + 1);
     unsigned long long m0, m1;  // the body's active bits: one load, independent of the pointers
     asm("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(m0), "=l"(m1) : "l"(a.bmask + 2 * b));
-    int64_t pk = 0, pke = 0;
     uint8_t own = 1;  // peer mode: 0 ghost, 1 owned, 2 owned with ghost copies on other ranks
-    if (halo && wi < nb_pad) pk = __ldg(a.push_ptr + b), pke = __ldg(a.push_ptr + b + 1);
     if (halo) own = __ldg(a.owned + b);
     // peer mode: ghost rows belong to their owners, who store into them from their own GPUs; a body with ghost copies
     // is done by a boundary CTA. Both are skipped by emptying the entry range (a select, not a branch on `own`: a
@@ -435,7 +435,11 @@ __global__ void __launch_bounds__(kBodyThreads)
       } else {
         st256(a.vel + b, D4{u.x, u.y, u.z, 0.0});
       }
-      if (halo) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
+      if (halo && own == 2) {  // fused velocity halo: the records also go straight into the peers' ghost rows (NVLink)
+        // (the list bounds are fetched here, by the few bodies that have ghost copies, and the loop is kept rolled:
+        // held across the entry loop, or unrolled, this rarely taken path cost every body of the pass 4 us per launch)
+        const int64_t pk = __ldg(a.push_ptr + b), pke = __ldg(a.push_ptr + b + 1);
+#pragma unroll 1
         for (int64_t k = pk; k < pke; ++k) {
           const uint32_t d = __ldg(a.push_dst + k);
           D4* dst = a.peer->vel[d >> 28];
