@@ -495,7 +495,9 @@ int mb200_comm_rank(const mb200_comm* comm);
 /* How the solver's per-iteration exchange runs: 1 = peer memory (CUDA IPC mappings over NVLink: the body / contact kernels
  * store velocity records and reduction totals straight into the peers' memory and signal with system-scope flags; chosen
  * automatically at the first distributed build when every rank could map every other rank), 0 = NCCL send/recv +
- * all-gather (fallback; forced with the environment variable MB200_DIST_EXCHANGE=nccl). Valid after the first step. */
+ * all-gather (fallback; forced with the environment variable MB200_DIST_EXCHANGE=nccl). Valid after the first step.
+ * MB200_DIST_EXCHANGE=peer additionally takes the peer-memory kernels when the communicator has a single rank (no peer
+ * to exchange with: a way to test and time those kernels on one GPU). */
 int mb200_comm_exchange_mode(const mb200_comm* comm);
 
 /* One collision timestep of the bodies distributed over the ranks. owned_bodies: device arrays of the bodies THIS rank owns

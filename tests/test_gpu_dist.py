@@ -78,6 +78,24 @@ def test_world1_distributed_step_equals_single_gpu_step(cuda, kind):
             assert np.array_equal(x[0], y[0]) and (x[1] is None or np.array_equal(x[1], y[1]))
 
 
+@pytest.mark.parametrize("kind", ["rods", "spheres"])
+def test_world1_peer_memory_kernels_equal_single_gpu_step(cuda, kind, monkeypatch):
+    """MB200_DIST_EXCHANGE=peer with ONE rank takes the peer-memory forms of the solver's kernels (body pass with the
+    ownership / boundary / push-list code, rate pass with the halo wait, coherent velocity loads and the in-kernel
+    reduction through the control block) without a second GPU: they must reproduce the single-GPU step bit for bit.
+    (The exchange between real peers is covered by the world 2 / 4 / 8 tests below.)"""
+    from mundy_b200 import dist as mbd
+    monkeypatch.setenv("MB200_DIST_EXCHANGE", "peer")
+    comm = mbd.Comm()
+    for fixed in (6, -1):
+        a = _run(kind, 4000, 3, fixed, "cuda:0")
+        b = _run(kind, 4000, 3, fixed, "cuda:0", comm)
+        for x, y in zip(a, b):
+            assert x[2:] == y[2:]
+            assert np.array_equal(x[0], y[0]) and (x[1] is None or np.array_equal(x[1], y[1]))
+    assert comm.exchange_mode == "peer"
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
