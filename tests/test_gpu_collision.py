@@ -91,6 +91,37 @@ def test_neighbor_links_candidates_and_filter(cuda, maker, kw, buffer):
         assert np.array_equal(host(links.pairs()), kept)
 
 
+def test_links_of_crowded_bodies(cuda):
+    """Bodies with more links than the count pass caches (16 with the shape filter, 48 without) are found again by the
+    fill pass: a sheaf of rods through one point inside a dilute suspension, and a heap of coincident spheres."""
+    from mundy_b200 import ops
+    w = wl.rods(3000, phi=0.05)
+    rng = np.random.default_rng(21)
+    k = 40
+    sheaf = rng.choice(3000, size=k, replace=False)
+    centre = w["center"].mean(axis=0)
+    w["center"][sheaf] = centre + rng.uniform(-0.05, 0.05, (k, 3))  # random orientations, (almost) one centre
+    S = oracle.search_radii(w["radius"], 0.5, w["kind"], w["length"])
+    want = oracle.search(w["center"], S)
+    b, _ = bodies_of(w)
+    links = ops.NeighborLinks().set_search_buffer(0.5)
+    assert links.generate(b)
+    got = host(links.pairs())
+    assert np.array_equal(got, want)
+    assert np.bincount(got[:, 0]).max() > 48
+    links.set_search_filter(ops.NeighborLinks.FILTER_SHAPE_DISTANCE)
+    assert links.generate(b)
+    kept = oracle.filter_shape_distance(want, w["center"], w["quat"], w["radius"], w["length"], w["kind"], 1.0)
+    got = host(links.pairs())
+    assert np.array_equal(got, kept)
+    # pairs are stored with the lower Morton index first: count per first body in the library's own order
+    assert np.bincount(np.unique(got, axis=0, return_inverse=True)[1]).max() == 1 and len(kept) >= k * (k - 1) // 2
+    # coincident spheres: every pair is a link, up to 59 per body
+    pos = np.zeros((60, 3))
+    got = host(ops.search_pairs(dev(pos), dev(np.ones(60))))
+    assert len(got) == 60 * 59 // 2 and np.array_equal(got, oracle.search(pos, np.ones(60), brute=True))
+
+
 def test_rebuild_trigger(cuda):
     """generate() returns false until some body moved more than half the buffer (GenNeighborLinkers.hpp:603-615)."""
     from mundy_b200 import ops
