@@ -284,10 +284,14 @@ constexpr int kChunk = MB200_BODY_CHUNK;
 // against 66 us at ptxas' own 72 registers: the spills go through the same load/store path as the gathers.)
 // HALO: the peer-memory multi-GPU form (ownership classes, boundary bodies first, remote stores, early halo flag); a
 // template parameter so that the single-GPU kernel does not carry its registers (72 against 92).
-// (axial arms, peer mode: six CTAs per SM, i.e. at most 80 registers, which the single-GPU form takes anyway: the peer-mode form
-// would take 84 and lose a CTA)
+// Resident CTAs per SM, axial arms (the kernel waits on gathers: warps in flight matter more than a few spilled words).
+// Single-GPU form: 7 (72 registers, 44 bytes of spills): 69.2 -> 66.5 us at cfg3 (8 CTAs / 64 registers: 66.9 us; left to
+// the compiler it takes 80 registers, 6 CTAs). Peer-mode form: MB200_BODY_CTAS_HALO (it would take 84 registers and drop to 5).
+#ifndef MB200_BODY_CTAS_HALO
+#define MB200_BODY_CTAS_HALO 6
+#endif
 template <int ARM, int MODE, bool FINAL, bool HALO>
-__global__ void __launch_bounds__(kBodyThreads, (ARM == ARM_AXIAL && HALO) ? 6 : 0)
+__global__ void __launch_bounds__(kBodyThreads, (ARM == ARM_AXIAL) ? (HALO ? MB200_BODY_CTAS_HALO : 7) : 0)
     body_pass_kernel(LcpArgs a, int first, double* __restrict__ F, double* __restrict__ T, double* __restrict__ U,
                      double* __restrict__ W, const double* __restrict__ U_ext, const double* __restrict__ W_ext) {
   if (!FINAL && a.state_blk->done) return;
