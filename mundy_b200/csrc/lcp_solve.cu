@@ -286,9 +286,10 @@ constexpr int kChunk = MB200_BODY_CHUNK;
 // template parameter so that the single-GPU kernel does not carry its registers (72 against 92).
 // Resident CTAs per SM, axial arms (the kernel waits on gathers: warps in flight matter more than a few spilled words).
 // Single-GPU form: 7 (72 registers, 44 bytes of spills): 69.2 -> 66.5 us at cfg3 (8 CTAs / 64 registers: 66.9 us; left to
-// the compiler it takes 80 registers, 6 CTAs). Peer-mode form: MB200_BODY_CTAS_HALO (it would take 84 registers and drop to 5).
+// the compiler it takes 80 registers, 6 CTAs). Peer-mode form (left alone: 84 registers, 5 CTAs): also 7, 72 registers with
+// 68 bytes of spills: 69.9 -> 68.8 us in a one-rank run of the peer-mode kernels (6 CTAs / 80 registers: 69.9 us).
 #ifndef MB200_BODY_CTAS_HALO
-#define MB200_BODY_CTAS_HALO 6
+#define MB200_BODY_CTAS_HALO 7
 #endif
 template <int ARM, int MODE, bool FINAL, bool HALO>
 __global__ void __launch_bounds__(kBodyThreads, (ARM == ARM_AXIAL) ? (HALO ? MB200_BODY_CTAS_HALO : 7) : 0)
