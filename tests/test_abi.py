@@ -64,3 +64,28 @@ def test_compute_fails_loudly_without_gpu():
     assert _capi.lib.mb200_neighbor_links_set_search_buffer(h, 0.5) == 0
     assert _capi.lib.mb200_neighbor_links_count(h) == 0
     assert _capi.lib.mb200_neighbor_links_destroy(h) == 0
+
+
+def test_header_constants_match_the_python_side():
+    """Limits that the header states and the harness repeats."""
+    from mundy_b200 import dist as mbd
+    from mundy_b200 import ops
+    text = open(HEADER).read()
+    assert int(re.search(r"#define MB200_NO_ALLOC_MAX_BODIES (\d+)", text).group(1)) == ops.NO_ALLOC_MAX_BODIES
+    src = open(os.path.join(ROOT, "mundy_b200", "csrc", "repartition.cu")).read()
+    assert int(re.search(r"kHilbertBits = (\d+)", src).group(1)) == mbd.HILBERT_BITS
+    assert 3 * mbd.HILBERT_BITS - int(re.search(r"kBucketBits = (\d+)", src).group(1)) == mbd.BUCKET_SHIFT
+
+
+def test_documented_environment_switches_exist_in_the_sources():
+    """INTEGRATION.md's table of switches against the getenv calls of the library and of bench.py."""
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    table = doc[doc.index("## Environment switches"):doc.index("## Stage timers")]
+    documented = set(re.findall(r"`(MB200_[A-Z_0-9]+)", table))
+    used = set()
+    for dp, _, files in os.walk(os.path.join(ROOT, "mundy_b200", "csrc")):
+        for f in files:
+            used |= set(re.findall(r'getenv\("(MB200_[A-Z_0-9]+)"\)', open(os.path.join(dp, f)).read()))
+    used |= {v for v in re.findall(r'environ\.get\("(MB200_[A-Z_0-9]+)"\)', open(os.path.join(ROOT, "bench.py")).read())
+             if v != "MB200_BENCH_VERBOSE"}
+    assert documented == used, sorted(documented ^ used)
